@@ -1,0 +1,176 @@
+/*
+ * rtc_b200.h -- C ABI of librtc_b200.so, the B200-native render loop.
+ *
+ * The reference has no plugin / FFI interface: its render step is the inline
+ * pthread fan-out of main() (reference main.c:285-302, 12 x rowThread,
+ * main.c:81-104).  render_cuda() is the drop-in for exactly those lines: same
+ * inputs (Scene by value -> pointer, the camera basis of main.c:252-255, the
+ * Triangle[] the loaders fill, width/height/maxBounce globals of main.c:10-12)
+ * and the same output (Color image[width*height], RGB8, row 0 on top,
+ * main.c:100,246), ready for the unchanged image writer call at main.c:305.
+ *
+ * Everything is plain C: pointers and sizes, no C++ or torch types.  All
+ * compute runs in hand-written CUDA kernels for sm_100a; there is NO CPU
+ * fallback -- without a usable GPU every entry point returns an error code.
+ */
+#ifndef RTC_B200_H
+#define RTC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include "rtc_types.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- error codes (the library never calls exit(); reference exits: SURVEY 5) */
+#define RTC_OK 0
+#define RTC_ERR_ARG 1      /* NULL / negative / inconsistent argument           */
+#define RTC_ERR_NO_GPU 2   /* no CUDA device, or not enough devices for ngpus   */
+#define RTC_ERR_CUDA 3     /* a CUDA runtime call failed (message on stderr)    */
+#define RTC_ERR_NCCL 4     /* libnccl missing or a NCCL call failed             */
+#define RTC_ERR_NOMEM 5
+
+/* ---- how the image is split over GPUs ------------------------- */
+#define RTC_SPLIT_TILES 0   /* interleaved row bands per GPU, ncclAllGather     */
+#define RTC_SPLIT_SAMPLES 1 /* disjoint sample sub-streams per GPU, float reduce */
+
+/* ---- RenderParams.flags --------------------------------------------------- */
+#define RTC_FLAG_COUNT_EXITS 1u /* fill RenderStats.tri_exit (slower kernel)     */
+#define RTC_FLAG_EXACT_ONLY 2u  /* disable the conservative FMA pre-filter: every
+                                   ray-triangle pair runs the reference's own
+                                   operation sequence (validation mode)          */
+
+/* counters a caller can ask for; replaces the reference's printf progress */
+typedef struct RenderStats {
+    uint64_t rays;         /* closest-hit sweeps (calls of calculateRayCollision, raytracing.c:270) */
+    uint64_t tri_pairs;    /* ray-triangle pairs tested = rays * ntris          */
+    uint64_t sphere_pairs; /* ray-sphere pairs tested                            */
+    uint64_t tri_exit[6];  /* pairs by reference exit: cull, det, u, v, dst, hit (RTC_FLAG_COUNT_EXITS) */
+    uint64_t hit_pixels;   /* pixels whose primary ray hit (only if out_primary_id != NULL) */
+    float upload_ms;       /* flatten + host->device of the scene               */
+    float kernel_ms;       /* device time of the render kernels, max over GPUs  */
+    float gather_ms;       /* NCCL gather / reduce + un-interleave              */
+    float download_ms;     /* device->host of the image                         */
+    int32_t kernels_launched;
+    int32_t ngpus_used;
+} RenderStats;
+
+/*
+ * What the reference keeps in globals and file-statics:
+ *   tris/ntris          raytracing.c's private triangles[]/triangleCount (scene.h:21-22)
+ *   spheres/nspheres    scene.h:17-20 (one hard-coded sphere); used when trianglesOnly == 0
+ *   width,height        main.c:10-11        maxBounce  main.c:12
+ *   spp                 scene.h:26 accumulationCount (compile-time 4000 there)
+ *   trianglesOnly       main.c:113,241
+ */
+typedef struct RenderParams {
+    const Triangle *tris;
+    int32_t ntris;
+    const Sphere *spheres;
+    int32_t nspheres;
+    int32_t width, height;
+    int32_t spp;
+    int32_t maxBounce;
+    int32_t trianglesOnly;
+    int32_t ngpus;           /* <= 1: one GPU (device 0 unless RTC_DEVICE is set) */
+    int32_t split_mode;      /* RTC_SPLIT_TILES | RTC_SPLIT_SAMPLES               */
+    int32_t nsplit;          /* <= 1: the reference's one RNG stream per pixel.
+                                G > 1: G sub-streams per pixel, sub-stream g seeded
+                                x + y*W + g*W*H renders samples [g*spp/G,(g+1)*spp/G),
+                                partial sums added in g order.          */
+    int32_t *out_primary_id; /* optional, width*height: -1 miss, -2-k sphere k, else triangle index */
+    RenderStats *stats;      /* optional */
+    uint32_t flags;
+} RenderParams;
+
+/*
+ * Render the whole frame into out_rgb (width*height*3 bytes, caller-owned host
+ * memory, RGB, row 0 = top: the reference's Color image[]).  Blocking; uploads
+ * the scene, renders on params->ngpus GPUs, gathers, downloads.  Replaces
+ * reference main.c:285-302.  Returns RTC_OK or an RTC_ERR_* code.
+ */
+int render_cuda(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const RenderParams *params);
+
+/* free cached device buffers / NCCL communicators held between calls */
+void render_cuda_shutdown(void);
+
+/* camera basis exactly as reference main.c:252-255 (IEEE float, no FMA) */
+void rtc_camera_look_at(const float origin[3], const float lookingAt[3], float fov, Camera *out);
+/* normalized() of reference moremath.c:12-18, e.g. for the sun (main.c:247) */
+void rtc_normalize(const float in[3], float out[3]);
+
+/* number of CUDA devices visible (0 if none / no driver) */
+int rtc_device_count(void);
+const char *rtc_last_error(void);
+const char *rtc_version(void);
+
+/* ---- device-resident API: scene stays in HBM, buffers are device pointers --
+ * Used by multi-process drivers (one process per GPU, e.g. under torchrun):
+ * each rank uploads the scene once, renders its share of the image into its
+ * own device buffer on its own stream, and the ranks exchange the parts with
+ * their collective library.                                                   */
+
+typedef struct RtcScene RtcScene; /* flattened SoA triangle/sphere/material buffers on one device */
+
+/* Flatten Triangle[] (AoS, 68 B) into 16-byte aligned SoA planes in HBM on
+ * `device` ({A,n.x} {B-A,n.y} {C-A,n.z} + material table).  Replaces nothing
+ * in the reference (it keeps AoS); consumes what raytracing.c:100-147 builds. */
+int rtc_scene_create(int device, const Triangle *tris, int32_t ntris, const Sphere *spheres, int32_t nspheres,
+                     RtcScene **out);
+void rtc_scene_destroy(RtcScene *scene);
+
+/* Which pixels one call renders, and where they land.  The output buffers are
+ * COMPACT: out_w x out_h pixels with
+ *     x = col_start + i * col_step                         (0 <= i < out_w)
+ *     y = row_start + (j / band_h) * row_step + j % band_h (0 <= j < out_h)
+ * so {0,1,0,1,1} over the full size is the whole image, {g*8, G*8, 0, 1, 8} is
+ * rank g's share of an 8-row band interleave over G ranks, and {0,60,0,60,1}
+ * is a sparse lattice.  Pixel results do not depend on the subset: every
+ * pixel owns its RNG seed x + y*width (reference main.c:95).                  */
+typedef struct RtcSubset {
+    int32_t row_start, row_step;
+    int32_t col_start, col_step;
+    int32_t band_h;
+} RtcSubset;
+
+typedef struct RtcDeviceJob {
+    int32_t width, height; /* of the FULL image (ray generation and seeds use these) */
+    int32_t spp, maxBounce, trianglesOnly;
+    int32_t nsplit;        /* total sub-streams per pixel (<= 1: reference)           */
+    int32_t split_first;   /* this call renders sub-streams [split_first,             */
+    int32_t split_count;   /*   split_first + split_count); 0 means all of them       */
+    RtcSubset subset;
+    int32_t out_w, out_h;  /* compact output size, see rtc_subset_size()              */
+    uint32_t flags;
+} RtcDeviceJob;
+
+/* compact size of a subset of a width x height image */
+void rtc_subset_size(int32_t width, int32_t height, const RtcSubset *s, int32_t *out_w, int32_t *out_h);
+
+/*
+ * Launch the render on `stream` (a cudaStream_t, NULL = default stream) of the
+ * scene's device; returns after the launches are queued.  Device pointers, any
+ * may be NULL:
+ *   d_rgb     out_w*out_h*3 bytes   quantised image (only meaningful when the call covers all sub-streams)
+ *   d_accum   out_w*out_h*3 floats  un-quantised sum of this call's sub-streams (sample split: reduce, then rtc_quantize_device)
+ *   d_ids     out_w*out_h int32     primary-hit ids
+ *   d_stats   RTC_DEVICE_STATS_WORDS uint64 counters, ADDED to (zero them first)
+ */
+#define RTC_DEVICE_STATS_WORDS 16
+int rtc_render_device(const RtcScene *scene, const Scene *sky, const Camera *cam, const RtcDeviceJob *job,
+                      uint8_t *d_rgb, float *d_accum, int32_t *d_ids, uint64_t *d_stats, void *stream);
+
+/* d_rgb[i] = quantise(d_accum[i]) with reference floatToUint (moremath.c:25-30); n = number of floats */
+int rtc_quantize_device(int device, const float *d_accum, uint8_t *d_rgb, size_t n, void *stream);
+
+/* number of kernels rtc_render_device launches for this job (for launch accounting) */
+int rtc_render_launch_count(const RtcScene *scene, const RtcDeviceJob *job, int want_ids);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* RTC_B200_H */

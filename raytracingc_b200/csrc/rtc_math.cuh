@@ -1,0 +1,155 @@
+// rtc_math.cuh -- device-side arithmetic of the render loop.
+//
+// Two families of operations live here and must not be mixed up:
+//
+//  * "exact" helpers (xmul, xadd, xsub, xdot, xcross, xnormalize, ...): every
+//    call is ONE IEEE binary32 round-to-nearest operation that nvcc can never
+//    contract into an FMA (__fmul_rn / __fadd_rn are contraction barriers).
+//    They reproduce, operation for operation and in the same order, what gcc
+//    emits for the reference's moremath.c on x86-64 (mulss/addss, no FMA,
+//    FLT_EVAL_METHOD 0).  Everything that decides a hit, moves a ray or feeds
+//    the RNG goes through these.  Where the reference widens to double
+//    (`1./x`, sqrt(), `2.*x`, smoothstep's tail, Box-Muller) the helper either
+//    widens too or uses the float instruction that is provably identical
+//    (double rounding is innocuous for +,-,*,/,sqrt when 53 >= 2*24+2).
+//
+//  * plain float expressions (a*b+c, fmaf): used only by the conservative
+//    pre-filter in rtc_kernels.cuh, whose result is a *superset* decision and
+//    never reaches the image.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rtc {
+
+struct f3 {
+    float x, y, z;
+};
+
+__device__ __forceinline__ f3 mk3(float x, float y, float z) { return f3{x, y, z}; }
+
+// ---- exact scalar ops -------------------------------------------------------
+__device__ __forceinline__ float xmul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float xadd(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float xsub(float a, float b) { return __fsub_rn(a, b); }
+// (float)(1./(double)a): correctly rounded float reciprocal (reference moremath.c:14, raytracing.c:197,287)
+__device__ __forceinline__ float xrcp(float a) { return __frcp_rn(a); }
+// (float)sqrt((double)a) == correctly rounded float sqrt (reference moremath.c:9, raytracing.c:173)
+__device__ __forceinline__ float xsqrt(float a) { return __fsqrt_rn(a); }
+__device__ __forceinline__ float xdiv(float a, float b) { return __fdiv_rn(a, b); }
+
+// ---- exact vec3 ops, reference moremath.c:33-87 -----------------------------
+__device__ __forceinline__ f3 xadd3(f3 a, f3 b) { return mk3(xadd(a.x, b.x), xadd(a.y, b.y), xadd(a.z, b.z)); }
+__device__ __forceinline__ f3 xsub3(f3 a, f3 b) { return mk3(xsub(a.x, b.x), xsub(a.y, b.y), xsub(a.z, b.z)); }
+__device__ __forceinline__ f3 xscale3(f3 a, float s) { return mk3(xmul(a.x, s), xmul(a.y, s), xmul(a.z, s)); }
+__device__ __forceinline__ f3 xmul3(f3 a, f3 b) { return mk3(xmul(a.x, b.x), xmul(a.y, b.y), xmul(a.z, b.z)); }
+// dot: (ax*bx + ay*by) + az*bz, left to right (moremath.c:34)
+__device__ __forceinline__ float xdot(f3 a, f3 b)
+{
+    return xadd(xadd(xmul(a.x, b.x), xmul(a.y, b.y)), xmul(a.z, b.z));
+}
+// cross (moremath.c:44-47)
+__device__ __forceinline__ f3 xcross(f3 u, f3 v)
+{
+    return mk3(xsub(xmul(u.y, v.z), xmul(u.z, v.y)), xsub(xmul(u.z, v.x), xmul(u.x, v.z)),
+               xsub(xmul(u.x, v.y), xmul(u.y, v.x)));
+}
+// normalized (moremath.c:7-18): len = sqrtf(sum), inv = 1/len, three multiplies
+__device__ __forceinline__ f3 xnormalize(f3 v)
+{
+    float len = xsqrt(xadd(xadd(xmul(v.x, v.x), xmul(v.y, v.y)), xmul(v.z, v.z)));
+    float inv = xrcp(len);
+    return xscale3(v, inv);
+}
+// reflect (moremath.c:80-83): dir - normal * (float)(2. * dot); the doubling is exact
+__device__ __forceinline__ f3 xreflect(f3 d, f3 n) { return xsub3(d, xscale3(n, xmul(2.0f, xdot(d, n)))); }
+// lerp (moremath.c:85-88): a*(1-t) + b*t
+__device__ __forceinline__ f3 xlerp(f3 a, f3 b, float t) { return xadd3(xscale3(a, xsub(1.0f, t)), xscale3(b, t)); }
+__device__ __forceinline__ float xclamp01(float x) { return x < 0.0f ? 0.0f : (x > 1.0f ? 1.0f : x); }
+// smoothstep (moremath.c:50-54): float quotient, float clamp, x*x in float,
+// (3. - 2.*x) and the final product in double, narrowed on return.
+__device__ __forceinline__ float xsmoothstep(float lo, float hi, float x)
+{
+    x = xclamp01(xdiv(xsub(x, lo), xsub(hi, lo)));
+    double t = __dsub_rn(3.0, __dmul_rn(2.0, (double)x));
+    return (float)__dmul_rn((double)xmul(x, x), t);
+}
+
+// ---- RNG, reference moremath.c:90-109 ---------------------------------------
+// RandomValue(): state = state*747796405 + 2891336453, PCG-RXS-M-XS output
+// hash, then (float)(r / 4294967295.0).  The double division is replaced by
+//     (float)( fma((double)r, 2^-32, (double)r) * 2^-32 )
+// which is bit-identical for all 2^32 values of r (both are r*2^-32*(1+eps),
+// 0 < eps << 2^-24 relative, strictly between r and the next float rounding
+// boundary; exhaustively verified by tests/test_rng_exhaustive.py via
+// tools/verify_rng_div.c).
+__device__ __forceinline__ uint32_t rng_next(uint32_t &state)
+{
+    state = state * 747796405u + 2891336453u;
+    uint32_t r = ((state >> ((state >> 28) + 4u)) ^ state) * 277803737u;
+    return (r >> 22) ^ r;
+}
+__device__ __forceinline__ float rng_to_unit(uint32_t r)
+{
+    double q = (double)r;
+    return (float)(__fma_rn(q, 2.3283064365386963e-10, q) * 2.3283064365386963e-10);
+}
+__device__ __forceinline__ float random_value(uint32_t &state) { return rng_to_unit(rng_next(state)); }
+
+// RandomValueNormalDistrubtion (moremath.c:98-103): all in double, narrowed
+// three times exactly where the reference's `float` locals narrow.
+__device__ __forceinline__ float random_normal(uint32_t &state)
+{
+    float u1 = random_value(state); // theta's draw comes first
+    float u2 = random_value(state);
+    float theta = (float)__dmul_rn(6.2831853, (double)u1); // 2 * 3.14159265, folded in double
+    float rho = (float)__dsqrt_rn(__dmul_rn(-2.0, log((double)u2)));
+    return (float)__dmul_rn((double)rho, cos((double)theta));
+}
+// RandomDiretion (moremath.c:105-109): x, then y, then z, then normalized
+__device__ __forceinline__ f3 random_direction(uint32_t &state)
+{
+    float x = random_normal(state);
+    float y = random_normal(state);
+    float z = random_normal(state);
+    return xnormalize(mk3(x, y, z));
+}
+
+// ---- sky, reference raytracing.c:151-160 ------------------------------------
+struct SkyParams {
+    f3 sun, horizon, zenith, ground;
+    float sunFocus, sunIntensity;
+};
+
+// glibc's powf is < 1 ulp; CUDA's powf is several ulp, so evaluate in double
+// and narrow.
+__device__ __forceinline__ float xpowf(float x, float y) { return (float)pow((double)x, (double)y); }
+
+__device__ __noinline__ f3 environment_light(f3 dir, const SkyParams &s)
+{
+    float t = xpowf(xsmoothstep(0.0f, 0.74f, -dir.y), 0.35f);
+    f3 grad = xlerp(s.horizon, s.zenith, t);
+    float d = xdot(dir, s.sun);
+    d = (d > 0.0f) ? d : 0.0f; // fmax(0, d): NaN -> 0
+    float sun = xmul(xpowf(d, s.sunFocus), s.sunIntensity);
+    float g2s = xsmoothstep(-0.01f, 0.0f, -dir.y);
+    float mask = dir.y < 0.0f ? 1.0f : 0.0f;
+    float sv = xmul(sun, mask);
+    f3 base = xlerp(s.ground, grad, g2s);
+    return mk3(xadd(base.x, sv), xadd(base.y, sv), xadd(base.z, sv));
+}
+
+// ---- quantise, reference moremath.c:25-30 ------------------------------------
+__device__ __forceinline__ uint32_t float_to_uint8(float f)
+{
+    if (f < 0.0f)
+        return 0u;
+    if (f >= 1.0f)
+        return 255u;
+    if (f != f)
+        return 0u; // NaN: x86 cvttss2si -> 0x80000000 -> low byte 0
+    return __float2uint_rz(xmul(f, 255.0f));
+}
+
+} // namespace rtc
