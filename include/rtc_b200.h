@@ -154,16 +154,26 @@ void rtc_subset_size(int32_t width, int32_t height, const RtcSubset *s, int32_t 
  * Launch the render on `stream` (a cudaStream_t, NULL = default stream) of the
  * scene's device; returns after the launches are queued.  Device pointers, any
  * may be NULL:
- *   d_rgb     out_w*out_h*3 bytes   quantised image (only meaningful when the call covers all sub-streams)
- *   d_accum   out_w*out_h*3 floats  un-quantised sum of this call's sub-streams (sample split: reduce, then rtc_quantize_device)
+ *   d_rgb     out_w*out_h*3 bytes   quantised image; written only when nsplit <= 1
+ *   d_accum   planes*out_w*out_h*3 floats: one un-quantised partial sum per sub-stream of this call
+ *             (planes = split_count, or nsplit - split_first when split_count == 0; 1 for the reference stream).
+ *             Required when nsplit > 1: gather the planes of all sub-streams in g order and finish with
+ *             rtc_sum_quantize_device, which adds them in that order (bit-exact for any GPU count).
  *   d_ids     out_w*out_h int32     primary-hit ids
- *   d_stats   RTC_DEVICE_STATS_WORDS uint64 counters, ADDED to (zero them first)
+ *   d_stats   RTC_DEVICE_STATS_WORDS uint64 counters, ADDED to (zero them first):
+ *             [0] rays [1] ray-triangle pairs [2] ray-sphere pairs [3..8] pairs by reference exit
+ *             (RTC_FLAG_COUNT_EXITS) [9] primary-hit pixels (d_ids != NULL) [10] pairs sent to the exact path
  */
 #define RTC_DEVICE_STATS_WORDS 16
 int rtc_render_device(const RtcScene *scene, const Scene *sky, const Camera *cam, const RtcDeviceJob *job,
                       uint8_t *d_rgb, float *d_accum, int32_t *d_ids, uint64_t *d_stats, void *stream);
 
-/* d_rgb[i] = quantise(d_accum[i]) with reference floatToUint (moremath.c:25-30); n = number of floats */
+/* total = plane_0 + plane_1 + ... (float adds in that order), then quantise with the reference's floatToUint
+ * (moremath.c:25-30).  d_planes: nplanes*n floats; d_rgb: n bytes or NULL; d_sum: n floats or NULL. */
+int rtc_sum_quantize_device(int device, const float *d_planes, int nplanes, size_t n, uint8_t *d_rgb, float *d_sum,
+                            void *stream);
+
+/* d_rgb[i] = quantise(d_accum[i]); n = number of floats */
 int rtc_quantize_device(int device, const float *d_accum, uint8_t *d_rgb, size_t n, void *stream);
 
 /* number of kernels rtc_render_device launches for this job (for launch accounting) */

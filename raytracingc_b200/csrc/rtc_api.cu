@@ -1,0 +1,725 @@
+// rtc_api.cu -- the C ABI of librtc_b200.so (include/rtc_b200.h).
+//
+// Host-side plumbing only: argument checks, device memory, launches, copies.
+// All arithmetic of the render loop is in rtc_kernels.cuh.  There is no CPU
+// rendering path here: without a CUDA device every entry point fails.
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "rtc_b200.h"
+#include "rtc_kernels.cuh"
+
+static_assert(sizeof(Triangle) == 68, "Triangle must match reference raytracing.h:41-45");
+static_assert(sizeof(Sphere) == 36, "Sphere must match reference raytracing.h:34-39");
+static_assert(sizeof(Scene) == 56, "Scene must match reference raytracing.h:7-11");
+static_assert(sizeof(Camera) == 52, "Camera is origin, ex, ey, ez, fov");
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    fprintf(stderr, "rtc_b200: %s\n", g_err);
+    return code;
+}
+
+#define CU(call)                                                                                      \
+    do {                                                                                              \
+        cudaError_t e_ = (call);                                                                      \
+        if (e_ != cudaSuccess)                                                                        \
+            return fail(RTC_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+rtc::f3 to3(const vec3 &v) { return rtc::f3{v.x, v.y, v.z}; }
+
+// host copy of reference normalized(), moremath.c:7-18 (built with -ffp-contract=off, no FMA on x86-64 baseline)
+void host_normalize(const float in[3], float out[3])
+{
+    float len = (float)sqrt((double)(in[0] * in[0] + in[1] * in[1] + in[2] * in[2]));
+    float inv = (float)(1. / (double)len);
+    out[0] = in[0] * inv;
+    out[1] = in[1] * inv;
+    out[2] = in[2] * inv;
+}
+
+void host_cross(const float u[3], const float v[3], float out[3])
+{
+    out[0] = u[1] * v[2] - u[2] * v[1];
+    out[1] = u[2] * v[0] - u[0] * v[2];
+    out[2] = u[0] * v[1] - u[1] * v[0];
+}
+
+} // namespace
+
+struct RtcScene {
+    int device = 0;
+    int ntris = 0, nsph = 0;
+    float4 *g0 = nullptr, *g1 = nullptr, *g2 = nullptr, *m0 = nullptr;
+    float *m1 = nullptr;
+    float4 *s0 = nullptr, *s1 = nullptr;
+    float *s2 = nullptr;
+    float *raw = nullptr; // staging of the caller's AoS records
+    size_t raw_bytes = 0;
+    int cap_tris = 0, cap_sph = 0;
+};
+
+extern "C" {
+
+const char *rtc_last_error(void) { return g_err; }
+const char *rtc_version(void) { return "rtc_b200 0.1 (sm_100a)"; }
+
+int rtc_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+void rtc_normalize(const float in[3], float out[3]) { host_normalize(in, out); }
+
+// reference main.c:252-255
+void rtc_camera_look_at(const float origin[3], const float lookingAt[3], float fov, Camera *out)
+{
+    float d[3] = {lookingAt[0] - origin[0], lookingAt[1] - origin[1], lookingAt[2] - origin[2]};
+    float ez[3], ex[3], ey[3], t[3];
+    const float up[3] = {0, -1, 0};
+    host_normalize(d, ez);
+    host_cross(ez, up, t);
+    host_normalize(t, ex);
+    host_cross(ez, ex, t);
+    host_normalize(t, ey);
+    out->origin = vec3{origin[0], origin[1], origin[2]};
+    out->ex = vec3{ex[0], ex[1], ex[2]};
+    out->ey = vec3{ey[0], ey[1], ey[2]};
+    out->ez = vec3{ez[0], ez[1], ez[2]};
+    out->fov = fov;
+}
+
+void rtc_subset_size(int32_t width, int32_t height, const RtcSubset *s, int32_t *out_w, int32_t *out_h)
+{
+    int cs = s->col_step > 0 ? s->col_step : 1, rs = s->row_step > 0 ? s->row_step : 1;
+    int bh = s->band_h > 0 ? s->band_h : 1;
+    int w = s->col_start < width ? (width - s->col_start + cs - 1) / cs : 0;
+    int h = 0;
+    for (int y0 = s->row_start; y0 < height; y0 += rs) {
+        int rows = height - y0 < bh ? height - y0 : bh;
+        h += rows;
+        if (rs < bh) { // overlapping bands are not a valid subset; treat as contiguous
+            h = height - s->row_start;
+            break;
+        }
+    }
+    *out_w = w;
+    *out_h = h;
+}
+
+void rtc_scene_destroy(RtcScene *sc)
+{
+    if (!sc)
+        return;
+    cudaSetDevice(sc->device);
+    cudaFree(sc->g0);
+    cudaFree(sc->g1);
+    cudaFree(sc->g2);
+    cudaFree(sc->m0);
+    cudaFree(sc->m1);
+    cudaFree(sc->s0);
+    cudaFree(sc->s1);
+    cudaFree(sc->s2);
+    cudaFree(sc->raw);
+    delete sc;
+}
+
+static int scene_reserve(RtcScene *sc, int ntris, int nsph)
+{
+    CU(cudaSetDevice(sc->device));
+    if (ntris > sc->cap_tris || !sc->g0) {
+        size_t nt = ntris > 0 ? ntris : 1;
+        cudaFree(sc->g0); cudaFree(sc->g1); cudaFree(sc->g2); cudaFree(sc->m0); cudaFree(sc->m1);
+        sc->g0 = sc->g1 = sc->g2 = sc->m0 = nullptr;
+        sc->m1 = nullptr;
+        CU(cudaMalloc(&sc->g0, sizeof(float4) * nt));
+        CU(cudaMalloc(&sc->g1, sizeof(float4) * nt));
+        CU(cudaMalloc(&sc->g2, sizeof(float4) * nt));
+        CU(cudaMalloc(&sc->m0, sizeof(float4) * nt));
+        CU(cudaMalloc(&sc->m1, sizeof(float) * nt));
+        sc->cap_tris = (int)nt;
+    }
+    if (nsph > sc->cap_sph || !sc->s0) {
+        size_t ns = nsph > 0 ? nsph : 1;
+        cudaFree(sc->s0); cudaFree(sc->s1); cudaFree(sc->s2);
+        sc->s0 = sc->s1 = nullptr;
+        sc->s2 = nullptr;
+        CU(cudaMalloc(&sc->s0, sizeof(float4) * ns));
+        CU(cudaMalloc(&sc->s1, sizeof(float4) * ns));
+        CU(cudaMalloc(&sc->s2, sizeof(float) * ns));
+        sc->cap_sph = (int)ns;
+    }
+    size_t need = sizeof(Triangle) * (size_t)(ntris > 0 ? ntris : 1) + sizeof(Sphere) * (size_t)(nsph > 0 ? nsph : 1);
+    if (need > sc->raw_bytes) {
+        cudaFree(sc->raw);
+        sc->raw = nullptr;
+        CU(cudaMalloc(&sc->raw, need));
+        sc->raw_bytes = need;
+    }
+    return RTC_OK;
+}
+
+// copy the caller's AoS arrays to the device and flatten them there (one-shot kernels), on `st`
+static int scene_upload(RtcScene *sc, const Triangle *tris, int ntris, const Sphere *spheres, int nsph,
+                        cudaStream_t st)
+{
+    int rc = scene_reserve(sc, ntris, nsph);
+    if (rc)
+        return rc;
+    sc->ntris = ntris;
+    sc->nsph = nsph;
+    float *raw_t = sc->raw;
+    float *raw_s = reinterpret_cast<float *>(reinterpret_cast<char *>(sc->raw) +
+                                             sizeof(Triangle) * (size_t)(ntris > 0 ? ntris : 1));
+    if (nsph > 0) {
+        CU(cudaMemcpyAsync(raw_s, spheres, sizeof(Sphere) * (size_t)nsph, cudaMemcpyHostToDevice, st));
+        rtc::flatten_spheres_kernel<<<(nsph + 127) / 128, 128, 0, st>>>(raw_s, nsph, sc->s0, sc->s1, sc->s2);
+        CU(cudaGetLastError());
+    }
+    if (ntris > 0) {
+        CU(cudaMemcpyAsync(raw_t, tris, sizeof(Triangle) * (size_t)ntris, cudaMemcpyHostToDevice, st));
+        rtc::flatten_kernel<<<(ntris + 127) / 128, 128, 0, st>>>(raw_t, ntris, sc->g0, sc->g1, sc->g2, sc->m0, sc->m1);
+        CU(cudaGetLastError());
+    }
+    return RTC_OK;
+}
+
+int rtc_scene_create(int device, const Triangle *tris, int32_t ntris, const Sphere *spheres, int32_t nspheres,
+                     RtcScene **out)
+{
+    if (!out || ntris < 0 || nspheres < 0 || (ntris > 0 && !tris) || (nspheres > 0 && !spheres))
+        return fail(RTC_ERR_ARG, "rtc_scene_create: bad arguments");
+    int ndev = rtc_device_count();
+    if (ndev <= 0)
+        return fail(RTC_ERR_NO_GPU, "no CUDA device: librtc_b200 has no CPU fallback");
+    if (device < 0 || device >= ndev)
+        return fail(RTC_ERR_NO_GPU, "device %d requested, %d visible", device, ndev);
+    RtcScene *sc = new RtcScene;
+    sc->device = device;
+    int rc = scene_upload(sc, tris, ntris, spheres, nspheres, 0);
+    if (rc == RTC_OK && cudaDeviceSynchronize() != cudaSuccess)
+        rc = fail(RTC_ERR_CUDA, "scene upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+    if (rc) {
+        rtc_scene_destroy(sc);
+        return rc;
+    }
+    *out = sc;
+    return RTC_OK;
+}
+
+} // extern "C"
+
+// ---- device-resident render -------------------------------------------------------
+
+namespace {
+
+int check_job(const RtcScene *sc, const Scene *sky, const Camera *cam, const RtcDeviceJob *job)
+{
+    if (!sc || !sky || !cam || !job)
+        return fail(RTC_ERR_ARG, "render: NULL argument");
+    if (job->width <= 0 || job->height <= 0 || job->spp <= 0 || job->maxBounce < 0)
+        return fail(RTC_ERR_ARG, "render: width/height/spp must be > 0, maxBounce >= 0 (got %d x %d, spp %d, b %d)",
+                    job->width, job->height, job->spp, job->maxBounce);
+    if (job->height / 2 == 0)
+        return fail(RTC_ERR_ARG, "render: height must be >= 2 (the reference divides by height/2, main.c:88)");
+    if (job->out_w < 0 || job->out_h < 0)
+        return fail(RTC_ERR_ARG, "render: negative output size");
+    return RTC_OK;
+}
+
+rtc::RenderArgs make_args(const RtcScene *sc, const Scene *sky, const Camera *cam, const RtcDeviceJob *job)
+{
+    rtc::RenderArgs a;
+    memset(&a, 0, sizeof a);
+    a.sc.g0 = sc->g0; a.sc.g1 = sc->g1; a.sc.g2 = sc->g2; a.sc.m0 = sc->m0; a.sc.m1 = sc->m1;
+    a.sc.ntris = sc->ntris;
+    a.sc.s0 = sc->s0; a.sc.s1 = sc->s1; a.sc.s2 = sc->s2;
+    a.sc.nsph = sc->nsph;
+    a.sky.sun = to3(sky->normalizedSunDirection);
+    a.sky.horizon = to3(sky->skyColorHorizon);
+    a.sky.zenith = to3(sky->skyColorZenith);
+    a.sky.ground = to3(sky->groundColor);
+    a.sky.sunFocus = sky->sunFocus;
+    a.sky.sunIntensity = sky->sunIntensity;
+    a.origin = to3(cam->origin);
+    a.ex = to3(cam->ex);
+    a.ey = to3(cam->ey);
+    a.ez = to3(cam->ez);
+    a.fov = cam->fov;
+    a.W = job->width;
+    a.H = job->height;
+    a.spp = job->spp;
+    a.maxBounce = job->maxBounce;
+    a.trianglesOnly = job->trianglesOnly;
+    a.nsplit = job->nsplit > 1 ? job->nsplit : 1;
+    a.split_first = job->split_first;
+    a.row_start = job->subset.row_start;
+    a.row_step = job->subset.row_step > 0 ? job->subset.row_step : 1;
+    a.col_start = job->subset.col_start;
+    a.col_step = job->subset.col_step > 0 ? job->subset.col_step : 1;
+    a.band_h = job->subset.band_h > 0 ? job->subset.band_h : 1;
+    a.out_w = job->out_w;
+    a.out_h = job->out_h;
+    return a;
+}
+
+int planes_of(const RtcDeviceJob *job)
+{
+    int G = job->nsplit > 1 ? job->nsplit : 1;
+    int cnt = job->split_count > 0 ? job->split_count : G - job->split_first;
+    return cnt;
+}
+
+} // namespace
+
+extern "C" {
+
+int rtc_render_launch_count(const RtcScene *sc, const RtcDeviceJob *job, int want_ids)
+{
+    (void)sc;
+    (void)want_ids;
+    if (!job || job->out_w <= 0 || job->out_h <= 0)
+        return 0;
+    return 1; // the fused render kernel; ids come from its first sweep
+}
+
+int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, const RtcDeviceJob *job,
+                      uint8_t *d_rgb, float *d_accum, int32_t *d_ids, uint64_t *d_stats, void *stream)
+{
+    int rc = check_job(sc, sky, cam, job);
+    if (rc)
+        return rc;
+    if (job->out_w == 0 || job->out_h == 0)
+        return RTC_OK;
+    int G = job->nsplit > 1 ? job->nsplit : 1;
+    int planes = planes_of(job);
+    if (job->split_first < 0 || planes <= 0 || job->split_first + planes > G)
+        return fail(RTC_ERR_ARG, "render: sub-stream range [%d,+%d) outside nsplit %d", job->split_first, planes, G);
+    if (G > 1 && !d_accum)
+        return fail(RTC_ERR_ARG, "render: nsplit > 1 needs d_accum (planes of partial sums)");
+    CU(cudaSetDevice(sc->device));
+    rtc::RenderArgs a = make_args(sc, sky, cam, job);
+    a.rgb = d_rgb;
+    a.accum = d_accum;
+    a.ids = d_ids;
+    a.stats = reinterpret_cast<unsigned long long *>(d_stats);
+    dim3 grid((job->out_w + rtc::CTA_W - 1) / rtc::CTA_W, (job->out_h + rtc::CTA_H - 1) / rtc::CTA_H, planes);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (job->flags & RTC_FLAG_COUNT_EXITS)
+        rtc::render_kernel<true><<<grid, rtc::CTA_THREADS, 0, st>>>(a);
+    else
+        rtc::render_kernel<false><<<grid, rtc::CTA_THREADS, 0, st>>>(a);
+    CU(cudaGetLastError());
+    return RTC_OK;
+}
+
+int rtc_sum_quantize_device(int device, const float *d_planes, int nplanes, size_t n, uint8_t *d_rgb, float *d_sum,
+                            void *stream)
+{
+    if (!d_planes || nplanes <= 0)
+        return fail(RTC_ERR_ARG, "sum_quantize: bad arguments");
+    if (n == 0)
+        return RTC_OK;
+    CU(cudaSetDevice(device));
+    rtc::sum_quantize_kernel<<<(unsigned)((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        d_planes, nplanes, n, d_rgb, d_sum);
+    CU(cudaGetLastError());
+    return RTC_OK;
+}
+
+int rtc_quantize_device(int device, const float *d_accum, uint8_t *d_rgb, size_t n, void *stream)
+{
+    return rtc_sum_quantize_device(device, d_accum, 1, n, d_rgb, nullptr, stream);
+}
+
+} // extern "C"
+
+// ---- render_cuda: the one-call drop-in for reference main.c:285-302 ------------------
+//
+// Single process, 1..8 devices.  Per device: upload + flatten the scene, render
+// this device's share (tile split: interleaved 8-row bands; sample split:
+// a contiguous range of RNG sub-streams), then gather on device 0 over NVLink
+// with ncclAllGather (NCCL is dlopen'ed so a 1-GPU caller has no NCCL
+// dependency), finish (un-interleave / ordered sum + quantise) and download.
+
+#include <dlfcn.h>
+#include <nccl.h>
+
+namespace {
+
+constexpr int BAND_H = 8;   // rows per interleaved band (two warp tiles)
+constexpr int MAX_GPUS = 16;
+
+struct NcclApi {
+    void *h = nullptr;
+    ncclResult_t (*CommInitAll)(ncclComm_t *, int, const int *) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+    bool load()
+    {
+        if (h)
+            return true;
+        const char *names[] = {"libnccl.so.2", "libnccl.so"};
+        for (const char *n : names)
+            if ((h = dlopen(n, RTLD_NOW | RTLD_LOCAL)))
+                break;
+        if (!h)
+            return false;
+#define SYM(field, name) field = reinterpret_cast<decltype(field)>(dlsym(h, name))
+        SYM(CommInitAll, "ncclCommInitAll");
+        SYM(CommDestroy, "ncclCommDestroy");
+        SYM(AllGather, "ncclAllGather");
+        SYM(GroupStart, "ncclGroupStart");
+        SYM(GroupEnd, "ncclGroupEnd");
+        SYM(GetErrorString, "ncclGetErrorString");
+#undef SYM
+        return CommInitAll && CommDestroy && AllGather && GroupStart && GroupEnd && GetErrorString;
+    }
+};
+
+struct DeviceSlot {
+    RtcScene *scene = nullptr;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr}; // upload begin, kernel begin, kernel end, gather end
+    void *part = nullptr;   // this device's share (bytes or float planes); with NCCL it is a slice of `all`
+    void *all = nullptr;    // gather buffer (G * part_bytes)
+    size_t all_bytes = 0;
+    int32_t *ids = nullptr;
+    size_t ids_bytes = 0;
+    unsigned long long *stats = nullptr;
+    uint8_t *img = nullptr; // device 0: final W*H*3 image
+    size_t img_bytes = 0;
+    float *accum = nullptr; // tile split with nsplit > 1: local sub-stream planes
+    size_t accum_bytes = 0;
+};
+
+struct Context {
+    std::mutex mu;
+    DeviceSlot slot[MAX_GPUS];
+    NcclApi nccl;
+    ncclComm_t comms[MAX_GPUS];
+    int ncomms = 0;
+} g_ctx;
+
+int slot_init(DeviceSlot &s, int dev)
+{
+    CU(cudaSetDevice(dev));
+    if (!s.scene) {
+        s.scene = new RtcScene;
+        s.scene->device = dev;
+    }
+    if (!s.stream)
+        CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    for (auto &e : s.ev)
+        if (!e)
+            CU(cudaEventCreate(&e));
+    if (!s.stats)
+        CU(cudaMalloc(&s.stats, sizeof(unsigned long long) * RTC_DEVICE_STATS_WORDS));
+    return RTC_OK;
+}
+
+int ensure(void **p, size_t *have, size_t need)
+{
+    if (need <= *have && *p)
+        return RTC_OK;
+    cudaFree(*p);
+    *p = nullptr;
+    *have = 0;
+    cudaError_t e = cudaMalloc(p, need ? need : 1);
+    if (e != cudaSuccess)
+        return fail(RTC_ERR_NOMEM, "cudaMalloc(%zu) failed: %s", need, cudaGetErrorString(e));
+    *have = need;
+    return RTC_OK;
+}
+
+// compact band-interleaved parts [G][max_h][W] elements -> image rows, on device 0
+template <typename T>
+__global__ void uninterleave_kernel(const T *__restrict__ all, T *__restrict__ img, int W_elems, int H, int G,
+                                    int band_h, size_t part_elems)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    size_t total = (size_t)W_elems * H;
+    if (i >= total)
+        return;
+    int y = (int)(i / W_elems), xe = (int)(i % W_elems);
+    int band = y / band_h, g = band % G, j = (band / G) * band_h + y % band_h;
+    img[i] = all[(size_t)g * part_elems + (size_t)j * W_elems + xe];
+}
+
+} // namespace
+
+extern "C" void render_cuda_shutdown(void)
+{
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    for (int i = 0; i < g_ctx.ncomms; ++i)
+        g_ctx.nccl.CommDestroy(g_ctx.comms[i]);
+    g_ctx.ncomms = 0;
+    for (int d = 0; d < MAX_GPUS; ++d) {
+        DeviceSlot &s = g_ctx.slot[d];
+        if (!s.scene && !s.stream)
+            continue;
+        cudaSetDevice(d);
+        rtc_scene_destroy(s.scene);
+        if (s.stream)
+            cudaStreamDestroy(s.stream);
+        for (auto &e : s.ev)
+            if (e)
+                cudaEventDestroy(e);
+        cudaFree(s.all);
+        cudaFree(s.ids);
+        cudaFree(s.stats);
+        cudaFree(s.img);
+        cudaFree(s.accum);
+        s = DeviceSlot();
+    }
+}
+
+namespace {
+
+#define NC(call)                                                                                   \
+    do {                                                                                           \
+        ncclResult_t r_ = (call);                                                                  \
+        if (r_ != ncclSuccess)                                                                     \
+            return fail(RTC_ERR_NCCL, "%s failed: %s", #call, g_ctx.nccl.GetErrorString(r_));      \
+    } while (0)
+
+int ensure_comms(int G)
+{
+    if (g_ctx.ncomms == G)
+        return RTC_OK;
+    if (!g_ctx.nccl.load())
+        return fail(RTC_ERR_NCCL, "ngpus = %d needs libnccl.so.2 (dlopen failed: %s)", G, dlerror());
+    for (int i = 0; i < g_ctx.ncomms; ++i)
+        g_ctx.nccl.CommDestroy(g_ctx.comms[i]);
+    g_ctx.ncomms = 0;
+    int devs[MAX_GPUS];
+    for (int i = 0; i < G; ++i)
+        devs[i] = i;
+    NC(g_ctx.nccl.CommInitAll(g_ctx.comms, G, devs));
+    g_ctx.ncomms = G;
+    return RTC_OK;
+}
+
+int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const RenderParams *p)
+{
+    const int W = p->width, H = p->height;
+    int G = p->ngpus > 1 ? p->ngpus : 1;
+    int ndev = rtc_device_count();
+    if (ndev <= 0)
+        return fail(RTC_ERR_NO_GPU, "no CUDA device: librtc_b200 has no CPU fallback");
+    if (G > ndev || G > MAX_GPUS)
+        return fail(RTC_ERR_NO_GPU, "ngpus = %d but %d device(s) visible", G, ndev);
+    int base = 0;
+    if (G == 1) {
+        const char *e = getenv("RTC_DEVICE");
+        if (e)
+            base = atoi(e);
+        if (base < 0 || base >= ndev)
+            return fail(RTC_ERR_NO_GPU, "RTC_DEVICE=%d but %d device(s) visible", base, ndev);
+    }
+    const bool samples = G > 1 && p->split_mode == RTC_SPLIT_SAMPLES;
+    int S = p->nsplit > 1 ? p->nsplit : 1;
+    if (samples) {
+        if (p->nsplit <= 1)
+            S = G;
+        if (S % G)
+            return fail(RTC_ERR_ARG, "sample split: nsplit (%d) must be a multiple of ngpus (%d)", S, G);
+    }
+    if (G > 1) {
+        int rc = ensure_comms(G);
+        if (rc)
+            return rc;
+    }
+    const size_t img_bytes = (size_t)W * H * 3;
+
+    // per-device jobs
+    RtcDeviceJob job[MAX_GPUS];
+    size_t part_bytes = 0; // gather slice per device
+    for (int g = 0; g < G; ++g) {
+        RtcDeviceJob &j = job[g];
+        memset(&j, 0, sizeof j);
+        j.width = W; j.height = H; j.spp = p->spp; j.maxBounce = p->maxBounce; j.trianglesOnly = p->trianglesOnly;
+        j.nsplit = S;
+        j.flags = p->flags;
+        if (samples) {
+            j.split_first = g * (S / G);
+            j.split_count = S / G;
+            j.subset = RtcSubset{0, 1, 0, 1, 1};
+        } else {
+            j.split_first = 0;
+            j.split_count = S;
+            j.subset = G > 1 ? RtcSubset{g * BAND_H, G * BAND_H, 0, 1, BAND_H} : RtcSubset{0, 1, 0, 1, 1};
+        }
+        rtc_subset_size(W, H, &j.subset, &j.out_w, &j.out_h);
+    }
+    if (samples)
+        part_bytes = (size_t)(S / G) * img_bytes * sizeof(float);
+    else
+        part_bytes = (size_t)job[0].out_h * W * 3; // device 0 owns the most rows
+
+    // launch everything, device by device (all asynchronous)
+    for (int g = 0; g < G; ++g) {
+        int dev = base + g;
+        DeviceSlot &s = g_ctx.slot[dev];
+        int rc = slot_init(s, dev);
+        if (rc)
+            return rc;
+        if ((rc = ensure(&s.all, &s.all_bytes, part_bytes * G)))
+            return rc;
+        s.part = static_cast<char *>(s.all) + part_bytes * g;
+        size_t npix = (size_t)job[g].out_w * job[g].out_h;
+        if (p->out_primary_id && (!samples || g == 0))
+            if ((rc = ensure(reinterpret_cast<void **>(&s.ids), &s.ids_bytes, npix * sizeof(int32_t))))
+                return rc;
+        if (!samples && S > 1)
+            if ((rc = ensure(reinterpret_cast<void **>(&s.accum), &s.accum_bytes, (size_t)S * npix * 3 * sizeof(float))))
+                return rc;
+        if (g == 0 && G > 1)
+            if ((rc = ensure(reinterpret_cast<void **>(&s.img), &s.img_bytes, img_bytes)))
+                return rc;
+        CU(cudaEventRecord(s.ev[0], s.stream));
+        CU(cudaMemsetAsync(s.stats, 0, sizeof(unsigned long long) * RTC_DEVICE_STATS_WORDS, s.stream));
+        if ((rc = scene_upload(s.scene, p->tris, p->ntris, p->spheres, p->nspheres, s.stream)))
+            return rc;
+        CU(cudaEventRecord(s.ev[1], s.stream));
+        int32_t *d_ids = (p->out_primary_id && (!samples || g == 0)) ? s.ids : nullptr;
+        if (samples) {
+            rc = rtc_render_device(s.scene, scene, cam, &job[g], nullptr, static_cast<float *>(s.part), d_ids,
+                                   reinterpret_cast<uint64_t *>(s.stats), s.stream);
+        } else if (S > 1) {
+            rc = rtc_render_device(s.scene, scene, cam, &job[g], nullptr, s.accum, d_ids,
+                                   reinterpret_cast<uint64_t *>(s.stats), s.stream);
+            if (!rc)
+                rc = rtc_sum_quantize_device(dev, s.accum, S, npix * 3, static_cast<uint8_t *>(s.part), nullptr,
+                                             s.stream);
+        } else {
+            rc = rtc_render_device(s.scene, scene, cam, &job[g], static_cast<uint8_t *>(s.part), nullptr, d_ids,
+                                   reinterpret_cast<uint64_t *>(s.stats), s.stream);
+        }
+        if (rc)
+            return rc;
+        CU(cudaSetDevice(dev));
+        CU(cudaEventRecord(s.ev[2], s.stream));
+    }
+
+    // gather over NVLink + finish on device 0
+    DeviceSlot &s0 = g_ctx.slot[base];
+    const uint8_t *d_final = static_cast<const uint8_t *>(s0.part);
+    if (G > 1) {
+        NC(g_ctx.nccl.GroupStart());
+        for (int g = 0; g < G; ++g) {
+            DeviceSlot &s = g_ctx.slot[g];
+            NC(g_ctx.nccl.AllGather(s.part, s.all, part_bytes, ncclUint8, g_ctx.comms[g], s.stream));
+        }
+        NC(g_ctx.nccl.GroupEnd());
+        CU(cudaSetDevice(base));
+        if (samples) {
+            int rc = rtc_sum_quantize_device(base, static_cast<const float *>(s0.all), S, img_bytes, s0.img, nullptr,
+                                             s0.stream);
+            if (rc)
+                return rc;
+        } else {
+            uninterleave_kernel<uint8_t><<<(unsigned)((img_bytes + 255) / 256), 256, 0, s0.stream>>>(
+                static_cast<const uint8_t *>(s0.all), s0.img, W * 3, H, G, BAND_H, part_bytes);
+            CU(cudaGetLastError());
+        }
+        d_final = s0.img;
+    }
+    CU(cudaSetDevice(base));
+    CU(cudaEventRecord(s0.ev[3], s0.stream));
+    CU(cudaMemcpyAsync(out_rgb, d_final, img_bytes, cudaMemcpyDeviceToHost, s0.stream));
+
+    // ids and counters
+    std::vector<int32_t> tmp;
+    unsigned long long tot[RTC_DEVICE_STATS_WORDS] = {0};
+    float up_ms = 0, k_ms = 0;
+    for (int g = 0; g < G; ++g) {
+        int dev = base + g;
+        DeviceSlot &s = g_ctx.slot[dev];
+        CU(cudaSetDevice(dev));
+        CU(cudaStreamSynchronize(s.stream));
+        unsigned long long h[RTC_DEVICE_STATS_WORDS];
+        CU(cudaMemcpy(h, s.stats, sizeof h, cudaMemcpyDeviceToHost));
+        for (int i = 0; i < RTC_DEVICE_STATS_WORDS; ++i)
+            tot[i] += h[i];
+        float a = 0, b = 0;
+        CU(cudaEventElapsedTime(&a, s.ev[0], s.ev[1]));
+        CU(cudaEventElapsedTime(&b, s.ev[1], s.ev[2]));
+        up_ms = a > up_ms ? a : up_ms;
+        k_ms = b > k_ms ? b : k_ms;
+        if (p->out_primary_id && (!samples || g == 0)) {
+            size_t npix = (size_t)job[g].out_w * job[g].out_h;
+            if (G == 1 || samples) {
+                CU(cudaMemcpy(p->out_primary_id, s.ids, npix * sizeof(int32_t), cudaMemcpyDeviceToHost));
+            } else {
+                tmp.resize(npix);
+                CU(cudaMemcpy(tmp.data(), s.ids, npix * sizeof(int32_t), cudaMemcpyDeviceToHost));
+                for (int j = 0; j < job[g].out_h; ++j) {
+                    int y = job[g].subset.row_start + (j / BAND_H) * job[g].subset.row_step + j % BAND_H;
+                    memcpy(p->out_primary_id + (size_t)y * W, tmp.data() + (size_t)j * W, sizeof(int32_t) * W);
+                }
+            }
+        }
+    }
+    if (p->stats) {
+        RenderStats *st = p->stats;
+        memset(st, 0, sizeof *st);
+        st->rays = tot[rtc::ST_RAYS];
+        st->tri_pairs = tot[rtc::ST_TRI_PAIRS];
+        st->sphere_pairs = tot[rtc::ST_SPH_PAIRS];
+        for (int e = 0; e < 6; ++e)
+            st->tri_exit[e] = tot[rtc::ST_EXIT0 + e];
+        st->hit_pixels = tot[rtc::ST_HIT_PIXELS];
+        st->upload_ms = up_ms;
+        st->kernel_ms = k_ms;
+        float gms = 0;
+        CU(cudaSetDevice(base));
+        CU(cudaEventElapsedTime(&gms, s0.ev[2], s0.ev[3]));
+        st->gather_ms = gms;
+        st->download_ms = 0; // folded into the caller's wall clock; the copy is asynchronous to ev[3]
+        st->ngpus_used = G;
+        int per_dev = 1 + (p->ntris > 0) + (p->nspheres > 0) + ((!samples && S > 1) ? 1 : 0);
+        st->kernels_launched = per_dev * G + (G > 1 ? 1 : 0);
+    }
+    return RTC_OK;
+}
+
+} // namespace
+
+extern "C" int render_cuda(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const RenderParams *p)
+{
+    if (!scene || !cam || !out_rgb || !p)
+        return fail(RTC_ERR_ARG, "render_cuda: NULL argument");
+    if (p->width <= 0 || p->height < 2 || p->spp <= 0 || p->maxBounce < 0)
+        return fail(RTC_ERR_ARG, "render_cuda: need width > 0, height >= 2, spp > 0, maxBounce >= 0");
+    if (p->ntris < 0 || p->nspheres < 0 || (p->ntris > 0 && !p->tris) || (p->nspheres > 0 && !p->spheres))
+        return fail(RTC_ERR_ARG, "render_cuda: triangle / sphere arrays inconsistent with their counts");
+    if (p->split_mode != RTC_SPLIT_TILES && p->split_mode != RTC_SPLIT_SAMPLES)
+        return fail(RTC_ERR_ARG, "render_cuda: unknown split_mode %d", p->split_mode);
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    return render_locked(scene, cam, out_rgb, p);
+}

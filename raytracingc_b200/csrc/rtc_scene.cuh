@@ -1,0 +1,53 @@
+// rtc_scene.cuh -- HBM layout of a flattened scene and the kernel argument block.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "rtc_math.cuh"
+
+namespace rtc {
+
+// Flattened scene (one per device).  The reference keeps Triangle[] as a 68-byte
+// array of structs and copies each one by value per test (raytracing.c:231);
+// here geometry is structure-of-arrays in three 16-byte-aligned planes so one
+// warp-uniform 128-bit load brings a third of a triangle:
+//     g0[i] = { A.x,  A.y,  A.z,  n.x }
+//     g1[i] = { AB.x, AB.y, AB.z, n.y }      AB = B - A   (raytracing.c:191, hoisted:
+//     g2[i] = { AC.x, AC.y, AC.z, n.z }      AC = C - A    the same float subtraction)
+// 48 B of geometry per triangle are read per (CTA sweep, triangle); the
+// material (20 B in the reference) is read once per closest hit:
+//     m0[i] = { color.r, color.g, color.b, emissionStrength }    m1[i] = smoothness
+// Spheres: s0[k] = { centre.xyz, r }, s1[k] = { color, emission }, s2[k] = smoothness.
+struct DeviceScene {
+    const float4 *g0, *g1, *g2;
+    const float4 *m0;
+    const float *m1;
+    int ntris;
+    const float4 *s0, *s1;
+    const float *s2;
+    int nsph;
+};
+
+struct RenderArgs {
+    DeviceScene sc;
+    SkyParams sky;
+    f3 origin, ex, ey, ez;
+    float fov;
+    int W, H;           // full image
+    int spp, maxBounce, trianglesOnly;
+    int nsplit;         // >= 1
+    int split_first;    // blockIdx.z + split_first = sub-stream index
+    // pixel subset -> compact output
+    int row_start, row_step, col_start, col_step, band_h;
+    int out_w, out_h;
+    uint8_t *rgb;       // [out_h][out_w][3] or null
+    float *accum;       // [planes][out_h][out_w][3] or null
+    int32_t *ids;       // [out_h][out_w] or null
+    unsigned long long *stats; // RTC_DEVICE_STATS_WORDS or null
+};
+
+// stats words
+enum { ST_RAYS = 0, ST_TRI_PAIRS = 1, ST_SPH_PAIRS = 2, ST_EXIT0 = 3, /* ..8 */ ST_HIT_PIXELS = 9, ST_SLOW_PAIRS = 10 };
+
+} // namespace rtc
