@@ -121,6 +121,10 @@ typedef struct RtcScene RtcScene; /* flattened SoA triangle/sphere/material buff
 int rtc_scene_create(int device, const Triangle *tris, int32_t ntris, const Sphere *spheres, int32_t nspheres,
                      RtcScene **out);
 void rtc_scene_destroy(RtcScene *scene);
+/* Re-upload (host -> device copy + flatten kernels, queued on `stream`) into an existing handle; buffers are
+ * reused when large enough.  The per-frame "scene changed" path of a resident renderer. */
+int rtc_scene_update(RtcScene *scene, const Triangle *tris, int32_t ntris, const Sphere *spheres, int32_t nspheres,
+                     void *stream);
 
 /* Which pixels one call renders, and where they land.  The output buffers are
  * COMPACT: out_w x out_h pixels with
@@ -178,6 +182,16 @@ int rtc_quantize_device(int device, const float *d_accum, uint8_t *d_rgb, size_t
 
 /* number of kernels rtc_render_device launches for this job (for launch accounting) */
 int rtc_render_launch_count(const RtcScene *scene, const RtcDeviceJob *job, int want_ids);
+
+/* parts [nparts][part_elems] -> image rows: part g holds the band_h-row bands g, g+nparts, ... of an image
+ * with `height` rows of `row_elems` elements (elem_size 1 or 4 bytes).  The un-interleave step after an
+ * all-gather of a tile split. */
+int rtc_uninterleave_device(int device, const void *d_parts, void *d_img, int elem_size, int row_elems, int height,
+                            int nparts, int band_h, size_t part_elems, void *stream);
+
+/* Dependent-free FFMA probe: measured FP32 peak of `device` in TFLOP/s (2 flop per FFMA), best of `reps`.
+ * The roofline denominator of the intersection kernel (MEASURED_PEAKS.json has no FP32 figure). */
+int rtc_fp32_peak_probe(int device, int reps, double *tflops, double *ms_best);
 
 #ifdef __cplusplus
 }

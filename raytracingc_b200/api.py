@@ -87,7 +87,8 @@ _lib = None
 # every symbol include/rtc_b200.h declares
 EXPORTS = ["render_cuda", "render_cuda_shutdown", "rtc_camera_look_at", "rtc_normalize", "rtc_device_count",
            "rtc_last_error", "rtc_version", "rtc_scene_create", "rtc_scene_destroy", "rtc_subset_size",
-           "rtc_render_device", "rtc_sum_quantize_device", "rtc_quantize_device", "rtc_render_launch_count"]
+           "rtc_render_device", "rtc_sum_quantize_device", "rtc_quantize_device", "rtc_render_launch_count",
+           "rtc_uninterleave_device", "rtc_fp32_peak_probe", "rtc_scene_update"]
 
 
 def load_library() -> C.CDLL:
@@ -113,6 +114,8 @@ def load_library() -> C.CDLL:
     lib.rtc_scene_create.argtypes = [C.c_int, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, P(C.c_void_p)]
     lib.rtc_scene_create.restype = C.c_int
     lib.rtc_scene_destroy.argtypes = [C.c_void_p]
+    lib.rtc_scene_update.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p]
+    lib.rtc_scene_update.restype = C.c_int
     lib.rtc_scene_destroy.restype = None
     lib.rtc_subset_size.argtypes = [C.c_int32, C.c_int32, P(RtcSubset), P(C.c_int32), P(C.c_int32)]
     lib.rtc_subset_size.restype = None
@@ -126,6 +129,11 @@ def load_library() -> C.CDLL:
     lib.rtc_quantize_device.restype = C.c_int
     lib.rtc_render_launch_count.argtypes = [C.c_void_p, P(RtcDeviceJob), C.c_int]
     lib.rtc_render_launch_count.restype = C.c_int
+    lib.rtc_uninterleave_device.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
+                                            C.c_int, C.c_size_t, C.c_void_p]
+    lib.rtc_uninterleave_device.restype = C.c_int
+    lib.rtc_fp32_peak_probe.argtypes = [C.c_int, C.c_int, P(C.c_double), P(C.c_double)]
+    lib.rtc_fp32_peak_probe.restype = C.c_int
     _lib = lib
     return lib
 
@@ -261,6 +269,15 @@ class DeviceScene:
                                                 stream or None))
         return j
 
+    def update(self, tris: np.ndarray, spheres: np.ndarray | None = None, stream: int = 0):
+        """Host -> device re-upload + flatten, queued on `stream` (arrays must stay alive until it has run)."""
+        tris = np.ascontiguousarray(tris, dtype=TRI_DTYPE)
+        sph = DEFAULT_SPHERES if spheres is None else np.ascontiguousarray(spheres, dtype=SPHERE_DTYPE)
+        self._keep = (tris, sph)
+        _check(load_library().rtc_scene_update(self.handle, tris.ctypes.data, len(tris), sph.ctypes.data, len(sph),
+                                               stream or None))
+        self.ntris, self.nspheres = len(tris), len(sph)
+
     def launch_count(self, job: DeviceJob, want_ids: bool = False) -> int:
         return load_library().rtc_render_launch_count(self.handle, C.byref(job.to_c()), int(want_ids))
 
@@ -279,3 +296,16 @@ class DeviceScene:
 def sum_quantize(device: int, d_planes: int, nplanes: int, n: int, d_rgb: int = 0, d_sum: int = 0, stream: int = 0):
     _check(load_library().rtc_sum_quantize_device(device, d_planes, nplanes, n, d_rgb or None, d_sum or None,
                                                   stream or None))
+
+
+def uninterleave(device: int, d_parts: int, d_img: int, elem_size: int, row_elems: int, height: int, nparts: int,
+                 band_h: int, part_elems: int, stream: int = 0):
+    _check(load_library().rtc_uninterleave_device(device, d_parts, d_img, elem_size, row_elems, height, nparts,
+                                                  band_h, part_elems, stream or None))
+
+
+def fp32_peak_tflops(device: int = 0, reps: int = 5) -> float:
+    """Measured dependent-free FFMA throughput of the device (2 flop per FFMA)."""
+    t, ms = C.c_double(), C.c_double()
+    _check(load_library().rtc_fp32_peak_probe(device, reps, C.byref(t), C.byref(ms)))
+    return t.value

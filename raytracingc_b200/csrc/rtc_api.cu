@@ -230,6 +230,14 @@ int rtc_scene_create(int device, const Triangle *tris, int32_t ntris, const Sphe
 
 } // extern "C"
 
+extern "C" int rtc_scene_update(RtcScene *sc, const Triangle *tris, int32_t ntris, const Sphere *spheres,
+                                int32_t nspheres, void *stream)
+{
+    if (!sc || ntris < 0 || nspheres < 0 || (ntris > 0 && !tris) || (nspheres > 0 && !spheres))
+        return fail(RTC_ERR_ARG, "rtc_scene_update: bad arguments");
+    return scene_upload(sc, tris, ntris, spheres, nspheres, static_cast<cudaStream_t>(stream));
+}
+
 // ---- device-resident render -------------------------------------------------------
 
 namespace {
@@ -723,3 +731,88 @@ extern "C" int render_cuda(const Scene *scene, const Camera *cam, uint8_t *out_r
     std::lock_guard<std::mutex> lk(g_ctx.mu);
     return render_locked(scene, cam, out_rgb, p);
 }
+
+// ---- small device utilities exposed for multi-process drivers and the benchmark ------
+
+namespace {
+
+// dependent-free FFMA throughput probe: 8 independent chains per thread
+__global__ void __launch_bounds__(256) ffma_probe_kernel(float *out, int iters, float a, float b)
+{
+    float r0 = threadIdx.x, r1 = r0 + 1, r2 = r0 + 2, r3 = r0 + 3, r4 = r0 + 4, r5 = r0 + 5, r6 = r0 + 6, r7 = r0 + 7;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            r0 = fmaf(r0, a, b); r1 = fmaf(r1, a, b); r2 = fmaf(r2, a, b); r3 = fmaf(r3, a, b);
+            r4 = fmaf(r4, a, b); r5 = fmaf(r5, a, b); r6 = fmaf(r6, a, b); r7 = fmaf(r7, a, b);
+        }
+    }
+    float s = r0 + r1 + r2 + r3 + r4 + r5 + r6 + r7;
+    if (s == 123.456f) // never true for the probe's inputs; keeps the chains alive
+        out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+} // namespace
+
+extern "C" {
+
+// Measured FP32 FFMA peak of `device` (MEASURED_PEAKS.json has no FP32 entry): best of `reps` launches.
+int rtc_fp32_peak_probe(int device, int reps, double *tflops, double *ms_best)
+{
+    if (!tflops)
+        return fail(RTC_ERR_ARG, "fp32_peak_probe: NULL");
+    if (rtc_device_count() <= device || device < 0)
+        return fail(RTC_ERR_NO_GPU, "fp32_peak_probe: device %d not visible", device);
+    CU(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    const int iters = 4096, threads = 256, blocks = prop.multiProcessorCount * 8 * 4;
+    float *buf = nullptr;
+    CU(cudaMalloc(&buf, sizeof(float) * (size_t)threads * blocks));
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    double best = 1e30;
+    for (int r = 0; r < (reps > 0 ? reps : 5) + 2; ++r) {
+        CU(cudaEventRecord(e0));
+        ffma_probe_kernel<<<blocks, threads>>>(buf, iters, 1.000001f, 0.5f);
+        CU(cudaEventRecord(e1));
+        CU(cudaEventSynchronize(e1));
+        float ms = 0;
+        CU(cudaEventElapsedTime(&ms, e0, e1));
+        if (r >= 2 && ms < best)
+            best = ms;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(buf);
+    double flops = 2.0 * 64.0 * iters * (double)threads * blocks;
+    *tflops = flops / (best * 1e-3) / 1e12;
+    if (ms_best)
+        *ms_best = best;
+    return RTC_OK;
+}
+
+// parts: [G][part_rows][row_elems] (rank g holds the 8-row bands g, g+G, ...) -> img [H][row_elems]
+int rtc_uninterleave_device(int device, const void *d_parts, void *d_img, int elem_size, int row_elems, int height,
+                            int nparts, int band_h, size_t part_elems, void *stream)
+{
+    if (!d_parts || !d_img || nparts <= 0 || band_h <= 0 || (elem_size != 1 && elem_size != 4))
+        return fail(RTC_ERR_ARG, "uninterleave: bad arguments");
+    CU(cudaSetDevice(device));
+    size_t total = (size_t)row_elems * height;
+    unsigned blocks = (unsigned)((total + 255) / 256);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (elem_size == 1)
+        uninterleave_kernel<uint8_t><<<blocks, 256, 0, st>>>(static_cast<const uint8_t *>(d_parts),
+                                                             static_cast<uint8_t *>(d_img), row_elems, height, nparts,
+                                                             band_h, part_elems);
+    else
+        uninterleave_kernel<uint32_t><<<blocks, 256, 0, st>>>(static_cast<const uint32_t *>(d_parts),
+                                                              static_cast<uint32_t *>(d_img), row_elems, height,
+                                                              nparts, band_h, part_elems);
+    CU(cudaGetLastError());
+    return RTC_OK;
+}
+
+} // extern "C"
