@@ -15,6 +15,7 @@
 
 #include "rtc_b200.h"
 #include "rtc_kernels.cuh"
+#include "rtc_fast.cuh"
 
 static_assert(sizeof(Triangle) == 68, "Triangle must match reference raytracing.h:41-45");
 static_assert(sizeof(Sphere) == 36, "Sphere must match reference raytracing.h:34-39");
@@ -73,6 +74,9 @@ struct RtcScene {
     float *raw = nullptr; // staging of the caller's AoS records
     size_t raw_bytes = 0;
     int cap_tris = 0, cap_sph = 0;
+    float4 *tab = nullptr; // per-frame edge-function table of the primary pre-filter (4 x float4 per triangle)
+    int cap_tab = 0;
+    int max_smem_optin = 0;
 };
 
 extern "C" {
@@ -142,6 +146,7 @@ void rtc_scene_destroy(RtcScene *sc)
     cudaFree(sc->s1);
     cudaFree(sc->s2);
     cudaFree(sc->raw);
+    cudaFree(sc->tab);
     delete sc;
 }
 
@@ -292,6 +297,85 @@ rtc::RenderArgs make_args(const RtcScene *sc, const Scene *sky, const Camera *ca
     return a;
 }
 
+// ---- fast-path eligibility and per-frame constants -----------------------------------
+
+double dot3d(const vec3 &a, const vec3 &b) { return (double)a.x * b.x + (double)a.y * b.y + (double)a.z * b.z; }
+
+// The pre-filter's error analysis (rtc_fast.cuh) assumes the camera basis main.c:252-255 builds:
+// orthonormal up to rounding.  Any other basis is rendered by the exact kernel.
+bool camera_is_orthonormal(const Camera *c)
+{
+    const double tol = 1e-3;
+    const vec3 *e[3] = {&c->ex, &c->ey, &c->ez};
+    for (int i = 0; i < 3; ++i) {
+        if (!(fabs(dot3d(*e[i], *e[i]) - 1.0) < tol))
+            return false;
+        for (int j = i + 1; j < 3; ++j)
+            if (!(fabs(dot3d(*e[i], *e[j])) < tol))
+                return false;
+    }
+    return std::isfinite(c->fov) && std::isfinite(c->origin.x) && std::isfinite(c->origin.y) &&
+           std::isfinite(c->origin.z);
+}
+
+// pixels per lane of the fast kernel, 0 = use the exact kernel
+int fast_path_R(const RtcScene *sc, const Camera *cam, const RtcDeviceJob *job)
+{
+    if (job->flags & (RTC_FLAG_EXACT_ONLY | RTC_FLAG_COUNT_EXITS))
+        return 0;
+    if (job->maxBounce < 1 || !camera_is_orthonormal(cam))
+        return 0;
+    if ((long long)job->width * job->height >= (1ll << 31))
+        return 0;
+    int R = 0;
+    const char *e = getenv("RTC_FAST_R");
+    if (e)
+        R = atoi(e);
+    if (e && R == 0)
+        return 0;
+    if (R != 1 && R != 2 && R != 4 && R != 8) {
+        long long px = (long long)job->out_w * job->out_h;
+        R = px >= 4000000 ? 8 : (px >= 1000000 ? 4 : 2);
+    }
+    int optin = sc->max_smem_optin;
+    if (optin == 0) {
+        cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, sc->device);
+        const_cast<RtcScene *>(sc)->max_smem_optin = optin;
+    }
+    while (R >= 1 && rtc::fast_smem_bytes(sc->ntris, R) > (size_t)optin)
+        R >>= 1;
+    return R; // 0 when even R = 1 does not fit: the scene is too large for the resident-table kernel
+}
+
+rtc::PrimaryFrame make_primary_frame(const Camera *cam, const RtcDeviceJob *job, int R)
+{
+    rtc::PrimaryFrame fr;
+    fr.origin = to3(cam->origin);
+    fr.ex = to3(cam->ex);
+    fr.ey = to3(cam->ey);
+    fr.ez = to3(cam->ez);
+    fr.fov = cam->fov;
+    const int W = job->width, H = job->height;
+    const double h2 = (double)(H / 2);
+    const double dxlo = (0 - W / 2) / h2, dxhi = (W - 1 - W / 2) / h2, dylo = (0 - H / 2) / h2,
+                 dyhi = (H - 1 - H / 2) / h2;
+    fr.dxmax = fmax(fabs(dxlo), fabs(dxhi));
+    fr.dymax = fmax(fabs(dylo), fabs(dyhi));
+    double dmax = 0;
+    for (double dx : {dxlo, dxhi})
+        for (double dy : {dylo, dyhi}) {
+            double v[3] = {cam->ex.x * dx + cam->ey.x * dy + (double)cam->ez.x * cam->fov,
+                           cam->ex.y * dx + cam->ey.y * dy + (double)cam->ez.y * cam->fov,
+                           cam->ex.z * dx + cam->ey.z * dy + (double)cam->ez.z * cam->fov};
+            dmax = fmax(dmax, sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]));
+        }
+    fr.Dmax = dmax * 1.001; // |D|^2 is convex in (dx, dy): the maximum over the image is at a corner
+    int cs = job->subset.col_step > 0 ? job->subset.col_step : 1;
+    fr.xstep = cs / h2;
+    fr.max_steps = R - 1;
+    return fr;
+}
+
 int planes_of(const RtcDeviceJob *job)
 {
     int G = job->nsplit > 1 ? job->nsplit : 1;
@@ -332,8 +416,43 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
     a.accum = d_accum;
     a.ids = d_ids;
     a.stats = reinterpret_cast<unsigned long long *>(d_stats);
-    dim3 grid((job->out_w + rtc::CTA_W - 1) / rtc::CTA_W, (job->out_h + rtc::CTA_H - 1) / rtc::CTA_H, planes);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int R = fast_path_R(sc, cam, job);
+    if (R > 0) {
+        RtcScene *msc = const_cast<RtcScene *>(sc); // the per-frame table is scratch owned by the handle
+        if (sc->ntris > msc->cap_tab || !msc->tab) {
+            cudaFree(msc->tab);
+            msc->tab = nullptr;
+            CU(cudaMalloc(&msc->tab, sizeof(float4) * 4 * (size_t)(sc->ntris > 0 ? sc->ntris : 1)));
+            msc->cap_tab = sc->ntris > 0 ? sc->ntris : 1;
+        }
+        rtc::PrimaryFrame fr = make_primary_frame(cam, job, R);
+        if (sc->ntris > 0) {
+            rtc::prepare_primary_kernel<<<(sc->ntris + 127) / 128, 128, 0, st>>>(a.sc, fr, msc->tab);
+            CU(cudaGetLastError());
+        }
+        size_t smem = rtc::fast_smem_bytes(sc->ntris, R);
+        dim3 fgrid((job->out_w + rtc::FAST_LX * R - 1) / (rtc::FAST_LX * R),
+                   (job->out_h + rtc::FAST_LY * rtc::FAST_WARPS - 1) / (rtc::FAST_LY * rtc::FAST_WARPS), planes);
+#define LAUNCH_FAST(RR)                                                                                         \
+    do {                                                                                                        \
+        CU(cudaFuncSetAttribute(rtc::render_fast_kernel<RR>, cudaFuncAttributeMaxDynamicSharedMemorySize,        \
+                                (int)smem));                                                                    \
+        rtc::render_fast_kernel<RR><<<fgrid, rtc::FAST_THREADS, smem, st>>>(a, msc->tab);                        \
+    } while (0)
+        if (R == 8)
+            LAUNCH_FAST(8);
+        else if (R == 4)
+            LAUNCH_FAST(4);
+        else if (R == 2)
+            LAUNCH_FAST(2);
+        else
+            LAUNCH_FAST(1);
+#undef LAUNCH_FAST
+        CU(cudaGetLastError());
+        return RTC_OK;
+    }
+    dim3 grid((job->out_w + rtc::CTA_W - 1) / rtc::CTA_W, (job->out_h + rtc::CTA_H - 1) / rtc::CTA_H, planes);
     if (job->flags & RTC_FLAG_COUNT_EXITS)
         rtc::render_kernel<true><<<grid, rtc::CTA_THREADS, 0, st>>>(a);
     else

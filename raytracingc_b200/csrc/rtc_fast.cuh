@@ -1,0 +1,350 @@
+// rtc_fast.cuh -- the production render kernel for scenes whose tables fit in
+// shared memory: screen-space conservative pre-filter for primary rays + the
+// reference's exact ray-triangle sequence for every pair that survives it.
+//
+// Why a pre-filter is legal (DESIGN.md "Exactness"): all primary rays share the
+// camera origin o, so for triangle (A, AB, AC, n) the reference's quantities are,
+// in real arithmetic, linear in the ray direction d:
+//     c   = d . n                    (cull:   c >= 0  -> miss)
+//     det = d . (AC x AB)            u*det = d . (AC x s)      s = o - A
+//     tq  = AC . (s x AB)  (const)   v*det = d . (s x AB)      t = tq / det
+// and d is a positive multiple of D = ex*dx + ey*dy + ez*fov, which is affine in
+// the pixel's (dx, dy).  So "the reference accepts this pair" implies four
+// affine functions of (dx, dy) are >= -(rounding slack):
+//     E0 = -(D.n)                  E1 = sg*(D.(AC x s))       sg = sign(tq)
+//     E2 = sg*(D.(s x AB))         E3 = sg*(D.(AC x AB)) - E1 - E2
+// prepare_primary_kernel computes their coefficients in double, adds a rigorous
+// bound of (reference rounding error + our evaluation error) to the constant
+// term, and the render kernel rejects a pair only if some E_k evaluates < 0.
+// Rejected pairs are pairs the reference rejects too; every other pair runs
+// tri_test_exact, so hit decisions, distances and ids are bit-identical.
+#pragma once
+
+#include "rtc_kernels.cuh"
+
+namespace rtc {
+
+struct PrimaryFrame {
+    f3 origin, ex, ey, ez;
+    float fov;
+    double dxmax, dymax; // max |dx|, |dy| over the full image
+    double Dmax;         // max |D| over the full image (a corner)
+    double xstep;        // col_step / (H/2): dx distance between the R pixels of a lane
+    int max_steps;       // R - 1
+};
+
+// table: 4 x float4 per triangle, one per edge function: {a, b, c + margin, a * xstep}
+__global__ void prepare_primary_kernel(const DeviceScene sc, const PrimaryFrame fr, float4 *__restrict__ tab)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= sc.ntris)
+        return;
+    const float4 p0 = sc.g0[i], p1 = sc.g1[i], p2 = sc.g2[i];
+    const f3 A = mk3(p0.x, p0.y, p0.z), AB = mk3(p1.x, p1.y, p1.z), AC = mk3(p2.x, p2.y, p2.z);
+    const f3 n = mk3(p0.w, p1.w, p2.w);
+    // exactly the reference's float values for a primary ray: s, q = s x AB, tq = AC . q
+    const f3 s = xsub3(fr.origin, A);
+    const f3 q = xcross(s, AB);
+    const float tq = xdot(AC, q);
+
+    const double u = 1.1920928955078125e-07; // 2^-23: twice the unit roundoff (safety factor 2)
+    double X[4][3];
+    double sg = tq > 0.0f ? 1.0 : -1.0;
+    const double M[3] = {(double)AC.y * s.z - (double)AC.z * s.y, (double)AC.z * s.x - (double)AC.x * s.z,
+                         (double)AC.x * s.y - (double)AC.y * s.x}; // AC x s
+    const double Nab[3] = {(double)AC.y * AB.z - (double)AC.z * AB.y, (double)AC.z * AB.x - (double)AC.x * AB.z,
+                           (double)AC.x * AB.y - (double)AC.y * AB.x}; // AC x AB
+    const double Q[3] = {(double)q.x, (double)q.y, (double)q.z};
+    const double N[3] = {(double)n.x, (double)n.y, (double)n.z};
+    for (int k = 0; k < 3; ++k) {
+        X[0][k] = -N[k];
+        X[1][k] = sg * M[k];
+        X[2][k] = sg * Q[k];
+        X[3][k] = sg * (Nab[k] - M[k] - Q[k]);
+    }
+    auto l1 = [](double x, double y, double z) { return fabs(x) + fabs(y) + fabs(z); };
+    const double n1 = l1(N[0], N[1], N[2]), s1 = l1(s.x, s.y, s.z), ab1 = l1(AB.x, AB.y, AB.z),
+                 ac1 = l1(AC.x, AC.y, AC.z), m1 = l1(M[0], M[1], M[2]), q1 = l1(Q[0], Q[1], Q[2]),
+                 nab1 = l1(Nab[0], Nab[1], Nab[2]);
+    // slack of the reference's own float evaluation relative to real arithmetic, in units of |D|:
+    //   direction error |d - D/|D||_inf <= 12u; a 3-term float dot errs <= 3u*sum|terms|; a float cross
+    //   component errs <= 2u*sum|terms|
+    const double B1 = 5.0 * s1 * ac1 + 12.0 * m1;
+    const double B2 = 15.0 * q1;
+    double delta[4];
+    delta[0] = 15.0 * n1;
+    delta[1] = B1;
+    delta[2] = B2;
+    delta[3] = 11.0 * ab1 * ac1 + 12.0 * nab1 + B1 + B2;
+    const double tiny = 1e-38 * ab1 * ac1; // products that underflow to -0 pass the reference's `< 0` tests
+
+    const double ex[3] = {fr.ex.x, fr.ex.y, fr.ex.z}, ey[3] = {fr.ey.x, fr.ey.y, fr.ey.z},
+                 ez[3] = {fr.ez.x, fr.ez.y, fr.ez.z};
+    bool usable = isfinite(tq) && tq != 0.0f;
+    float4 out[4];
+    for (int k = 0; k < 4; ++k) {
+        double a = ex[0] * X[k][0] + ex[1] * X[k][1] + ex[2] * X[k][2];
+        double b = ey[0] * X[k][0] + ey[1] * X[k][1] + ey[2] * X[k][2];
+        double c = (double)fr.fov * (ez[0] * X[k][0] + ez[1] * X[k][1] + ez[2] * X[k][2]);
+        double range = fabs(a) * fr.dxmax + fabs(b) * fr.dymax + fabs(c);
+        // our own evaluation: coefficient rounding, two FMAs, up to max_steps incremental adds
+        double eps = (8.0 + 2.0 * fr.max_steps) * range;
+        double margin = 2.0 * u * (delta[k] * fr.Dmax + eps) + tiny * fr.Dmax + 1e-30;
+        double cm = c + margin;
+        out[k] = make_float4((float)a, (float)b, (float)cm, (float)(a * fr.xstep));
+        // too large / too small to reason about in float: let the exact path decide
+        if (!isfinite(a) || !isfinite(b) || !isfinite(cm) || range > 1e30 || margin > 1e30)
+            usable = false;
+    }
+    if (!usable) {
+        if (isfinite(tq) && tq == 0.0f) {
+            // t = tq * inv = +-0 -> `dst < EPSILON` holds: a primary ray can never hit this triangle
+            for (int k = 0; k < 4; ++k)
+                out[k] = make_float4(0.f, 0.f, -1.f, 0.f);
+        } else {
+            for (int k = 0; k < 4; ++k)
+                out[k] = make_float4(0.f, 0.f, 1.f, 0.f); // always pass
+        }
+    }
+    for (int k = 0; k < 4; ++k)
+        tab[4 * i + k] = out[k];
+}
+
+// ---- fast render kernel -------------------------------------------------------------
+// Lane layout: 8 x 4 lanes per warp, each lane owns R horizontally adjacent pixels
+// (warp tile 8R x 4); a CTA is 4 warps stacked in y (CTA tile 8R x 16).
+constexpr int FAST_LX = 8, FAST_LY = 4, FAST_WARPS = 4, FAST_THREADS = 32 * FAST_WARPS;
+
+struct FastSmem {
+    float4 *F;      // [4 * ntris] edge-function table
+    float4 *G;      // [3 * ntris] geometry planes g0,g1,g2 interleaved
+    float4 *state;  // [THREADS * R] {rng bits, acc.x, acc.y, acc.z}
+    float2 *hit;    // [THREADS * R] {best, id bits}
+};
+
+__host__ __device__ inline size_t fast_smem_bytes(int ntris, int R)
+{
+    return (size_t)ntris * 7 * sizeof(float4) + (size_t)FAST_THREADS * R * (sizeof(float4) + sizeof(float2));
+}
+
+// primary ray direction of pixel (x, y): main.c:88-93, exact
+__device__ __forceinline__ f3 primary_dir(const RenderArgs &a, float dx, float dy)
+{
+    f3 d = xadd3(xadd3(xscale3(a.ex, dx), xscale3(a.ey, dy)), xscale3(a.ez, a.fov));
+    return xnormalize(d);
+}
+
+// general exact closest hit against the shared-memory tables (spheres from global)
+__device__ __noinline__ void closest_exact_smem(const RenderArgs &a, const float4 *__restrict__ G, int ntris, int nsph,
+                                                f3 o, f3 d, float &best, int &bestId)
+{
+    best = 999999.0f;
+    bestId = -1;
+    for (int k = 0; k < nsph; ++k)
+        sphere_test_exact(o, d, __ldg(&a.sc.s0[k]), k, best, bestId);
+    unsigned dummy[1];
+#pragma unroll 2
+    for (int i = 0; i < ntris; ++i)
+        tri_test_exact<false>(o, d, G[3 * i], G[3 * i + 1], G[3 * i + 2], i, best, bestId, dummy);
+}
+
+template <int R>
+__global__ void __launch_bounds__(FAST_THREADS) render_fast_kernel(const RenderArgs a, const float4 *__restrict__ tab)
+{
+    extern __shared__ float4 smem_raw[];
+    const int ntris = a.sc.ntris;
+    const int nsph = a.trianglesOnly ? 0 : a.sc.nsph;
+    float4 *sF = smem_raw;
+    float4 *sG = sF + 4 * ntris;
+    float4 *sState = sG + 3 * ntris;
+    float2 *sHit = reinterpret_cast<float2 *>(sState + FAST_THREADS * R);
+
+    for (int i = threadIdx.x; i < 4 * ntris; i += FAST_THREADS)
+        sF[i] = tab[i];
+    for (int i = threadIdx.x; i < ntris; i += FAST_THREADS) {
+        sG[3 * i] = a.sc.g0[i];
+        sG[3 * i + 1] = a.sc.g1[i];
+        sG[3 * i + 2] = a.sc.g2[i];
+    }
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int ci0 = (blockIdx.x * FAST_LX + (lane % FAST_LX)) * R;
+    const int cj = (blockIdx.y * FAST_WARPS + warp) * FAST_LY + lane / FAST_LX;
+    const int g = a.split_first + blockIdx.z;
+    const int x0 = a.col_start + ci0 * a.col_step;
+    const int y = a.row_start + (cj / a.band_h) * a.row_step + (cj % a.band_h);
+    unsigned valid = 0;
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+        if (ci0 + r < a.out_w && cj < a.out_h)
+            valid |= 1u << r;
+
+    const float fh = (float)(a.H / 2);
+    const float dy = xdiv((float)(y - a.H / 2), fh);
+    const float dx0 = xdiv((float)(x0 - a.W / 2), fh);
+    auto dx_of = [&](int r) { return xdiv((float)(x0 + r * a.col_step - a.W / 2), fh); };
+
+    float4 *myState = sState + threadIdx.x; // slot r at myState[r * FAST_THREADS]
+    float2 *myHit = sHit + threadIdx.x;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        uint32_t seed = (uint32_t)(x0 + r * a.col_step + y * a.W) + (uint32_t)g * (uint32_t)(a.W * a.H);
+        myState[r * FAST_THREADS] = make_float4(__uint_as_float(seed), 0.f, 0.f, 0.f);
+    }
+
+    const int s0 = (int)((long long)g * a.spp / a.nsplit), s1 = (int)((long long)(g + 1) * a.spp / a.nsplit);
+    const float w = (float)(1.0 / (double)a.spp);
+    unsigned geom = 0;
+    unsigned long long nrays = 0, nslow = 0;
+
+    for (int s = s0; s < s1; ++s) {
+        float best[R];
+        int id[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            best[r] = 999999.0f;
+            id[r] = -1;
+        }
+        if (nsph > 0) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                f3 d = primary_dir(a, dx_of(r), dy);
+                for (int k = 0; k < nsph; ++k)
+                    sphere_test_exact(a.origin, d, __ldg(&a.sc.s0[k]), k, best[r], id[r]);
+            }
+        }
+        // ---- primary sweep: conservative edge-function filter, exact test for survivors ----
+#pragma unroll 2
+        for (int i = 0; i < ntris; ++i) {
+            const float4 f0 = sF[4 * i], f1 = sF[4 * i + 1], f2 = sF[4 * i + 2], f3_ = sF[4 * i + 3];
+            float e0 = fmaf(f0.x, dx0, fmaf(f0.y, dy, f0.z));
+            float e1 = fmaf(f1.x, dx0, fmaf(f1.y, dy, f1.z));
+            float e2 = fmaf(f2.x, dx0, fmaf(f2.y, dy, f2.z));
+            float e3 = fmaf(f3_.x, dx0, fmaf(f3_.y, dy, f3_.z));
+            int acc = -1;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                acc &= (__float_as_int(e0) | __float_as_int(e1) | __float_as_int(e2) | __float_as_int(e3));
+                if (r + 1 < R) {
+                    e0 += f0.w;
+                    e1 += f1.w;
+                    e2 += f2.w;
+                    e3 += f3_.w;
+                }
+            }
+            if (__any_sync(0xffffffffu, acc >= 0)) {
+                if (acc >= 0) {
+                    const float4 p0 = sG[3 * i], p1 = sG[3 * i + 1], p2 = sG[3 * i + 2];
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        const float dxr = dx_of(r);
+                        const float t0 = fmaf(f0.x, dxr, fmaf(f0.y, dy, f0.z));
+                        const float t1 = fmaf(f1.x, dxr, fmaf(f1.y, dy, f1.z));
+                        const float t2 = fmaf(f2.x, dxr, fmaf(f2.y, dy, f2.z));
+                        const float t3 = fmaf(f3_.x, dxr, fmaf(f3_.y, dy, f3_.z));
+                        const int bits = __float_as_int(t0) | __float_as_int(t1) | __float_as_int(t2) | __float_as_int(t3);
+                        if (bits >= 0 && ((valid >> r) & 1u)) {
+                            unsigned dummy[1];
+                            f3 d = primary_dir(a, dxr, dy);
+                            tri_test_exact<false>(a.origin, d, p0, p1, p2, i, best[r], id[r], dummy);
+                            nslow++;
+                        }
+                    }
+                }
+            }
+        }
+        nrays += __popc(valid);
+
+        unsigned hits = 0;
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+            if (id[r] != -1 && ((valid >> r) & 1u)) {
+                hits |= 1u << r;
+                myHit[r * FAST_THREADS] = make_float2(best[r], __int_as_float(id[r]));
+            }
+        if (s == s0) {
+            geom = hits;
+            if (a.ids != nullptr && g == a.split_first) {
+#pragma unroll
+                for (int r = 0; r < R; ++r)
+                    if ((valid >> r) & 1u)
+                        a.ids[(size_t)cj * a.out_w + ci0 + r] = id[r];
+            }
+        }
+        // ---- paths of the pixels whose primary ray hit (rare): bounce loop with exact sweeps ----
+        while (hits) {
+            const int r = __ffs(hits) - 1;
+            hits &= hits - 1;
+            float4 st = myState[r * FAST_THREADS];
+            const float2 h = myHit[r * FAST_THREADS];
+            Lane L;
+            L.pos = a.origin;
+            L.dir = primary_dir(a, dx_of(r), dy);
+            L.tint = mk3(1.f, 1.f, 1.f);
+            L.light = mk3(0.f, 0.f, 0.f);
+            L.rng = __float_as_uint(st.x);
+            L.bounce = 0;
+            float bst = h.x;
+            int bid = __float_as_int(h.y);
+            while (!shade(L, a, bst, bid)) {
+                closest_exact_smem(a, sG, ntris, nsph, L.pos, L.dir, bst, bid);
+                nrays++;
+            }
+            st.x = __uint_as_float(L.rng);
+            st.y = xadd(st.y, xmul(L.light.x, w)); // main.c:99
+            st.z = xadd(st.z, xmul(L.light.y, w));
+            st.w = xadd(st.w, xmul(L.light.z, w));
+            myState[r * FAST_THREADS] = st;
+        }
+    }
+
+    // ---- finish: sky pixels receive spp identical contributions (same ray, no RNG draw) ----
+    for (int r = 0; r < R; ++r) {
+        if (!((valid >> r) & 1u))
+            continue;
+        const float4 st = myState[r * FAST_THREADS];
+        f3 acc = mk3(st.y, st.z, st.w);
+        if (!((geom >> r) & 1u)) {
+            f3 d = primary_dir(a, dx_of(r), dy);
+            f3 env = environment_light(d, a.sky);
+            f3 light = xadd3(mk3(0.f, 0.f, 0.f), xmul3(env, mk3(1.f, 1.f, 1.f))); // raytracing.c:291
+            f3 c = xscale3(light, w);
+            for (int s = s0; s < s1; ++s)
+                acc = xadd3(acc, c);
+        }
+        const size_t pix = (size_t)cj * a.out_w + ci0 + r;
+        if (a.accum != nullptr) {
+            float *p = a.accum + ((size_t)blockIdx.z * a.out_w * a.out_h + pix) * 3;
+            p[0] = acc.x;
+            p[1] = acc.y;
+            p[2] = acc.z;
+        }
+        if (a.rgb != nullptr && a.nsplit == 1) {
+            uint8_t *p = a.rgb + pix * 3;
+            p[0] = (uint8_t)float_to_uint8(acc.x);
+            p[1] = (uint8_t)float_to_uint8(acc.y);
+            p[2] = (uint8_t)float_to_uint8(acc.z);
+        }
+    }
+
+    if (a.stats != nullptr) {
+        unsigned long long hp = (g == a.split_first) ? __popc(geom) : 0, r_ = nrays, sl = nslow;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            r_ += __shfl_xor_sync(0xffffffffu, r_, o);
+            hp += __shfl_xor_sync(0xffffffffu, hp, o);
+            sl += __shfl_xor_sync(0xffffffffu, sl, o);
+        }
+        if (lane == 0) {
+            atomicAdd(&a.stats[ST_RAYS], r_);
+            atomicAdd(&a.stats[ST_TRI_PAIRS], r_ * (unsigned long long)ntris);
+            atomicAdd(&a.stats[ST_SPH_PAIRS], r_ * (unsigned long long)nsph);
+            atomicAdd(&a.stats[ST_SLOW_PAIRS], sl);
+            if (a.ids != nullptr)
+                atomicAdd(&a.stats[ST_HIT_PIXELS], hp);
+        }
+    }
+}
+
+} // namespace rtc

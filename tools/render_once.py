@@ -1,0 +1,20 @@
+#!/usr/bin/env python
+"""Render N frames of a bench workload through the C ABI (for ncu / quick timing); prints kernel ms."""
+import argparse
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import bench  # noqa: E402
+import raytracingc_b200 as rtc  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--workload", default="c4")
+ap.add_argument("--frames", type=int, default=2)
+ap.add_argument("--flags", type=int, default=0)
+a = ap.parse_args()
+scene, W, H, spp, bounce, tonly = bench.WORKLOADS[a.workload]
+tris = bench.load_tris(scene)
+for i in range(a.frames):
+    rgb, _, st = rtc.render(tris, W, H, spp, bounce, triangles_only=tonly, flags=a.flags)
+    print(f"{a.workload} frame {i}: kernel {st['kernel_ms']:.3f} ms, rays {st['rays']}, upload {st['upload_ms']:.3f} ms")
