@@ -124,7 +124,7 @@ struct FastSmem {
 
 __host__ __device__ inline size_t fast_smem_bytes(int ntris, int R)
 {
-    return (size_t)ntris * 7 * sizeof(float4) + (size_t)FAST_THREADS * R * (sizeof(float4) + sizeof(float2));
+    return (size_t)ntris * 7 * sizeof(float4) + (size_t)FAST_THREADS * R * (sizeof(float4) + sizeof(float2) + 1);
 }
 
 // primary ray direction of pixel (x, y): main.c:88-93, exact
@@ -132,6 +132,46 @@ __device__ __forceinline__ f3 primary_dir(const RenderArgs &a, float dx, float d
 {
     f3 d = xadd3(xadd3(xscale3(a.ex, dx), xscale3(a.ey, dy)), xscale3(a.ez, a.fov));
     return xnormalize(d);
+}
+
+// The reference's ray-triangle test arranged for SIMT: the values the reference computes up to
+// s.h (its c, det and s.h, same operations, same order) are evaluated straight-line for every pair,
+// which gives the scheduler independent work across unrolled triangles; the exits are then taken on
+// those exact values.  Two of them are decided without the division:
+//   * sign(s.h) != sign(det), |s.h| >= 1e-30, |det| <= 2^20  =>  u = fl(s.h * fl(1/det)) < 0   (no underflow to -0)
+//   * same sign and |s.h| > |det| * 1.00001                     =>  u > 1                       (margin >> 3 roundings)
+// Every other pair continues with the reference's remaining operations, so decisions are identical.
+__device__ __forceinline__ void tri_test_exact_sl(const f3 &o, const f3 &d, const float4 &p0, const float4 &p1,
+                                                  const float4 &p2, int idx, float &best, int &bestId)
+{
+    const f3 n = mk3(p0.w, p1.w, p2.w);
+    const f3 AB = mk3(p1.x, p1.y, p1.z), AC = mk3(p2.x, p2.y, p2.z);
+    const float c = xdot(d, n);
+    const f3 h = xcross(d, AC);
+    const float det = xdot(AB, h);
+    const f3 s = xsub3(o, mk3(p0.x, p0.y, p0.z));
+    const float sh = xdot(s, h);
+    const bool cont = !(c >= 0.0f) && !(-0.001f < det && det < 0.001f);
+    const float adet = fabsf(det), ash = fabsf(sh);
+    const bool opp = (__float_as_int(sh) ^ __float_as_int(det)) < 0;
+    const bool rej = opp ? (ash >= 1e-30f && adet <= 1048576.0f) : (ash > xmul(adet, 1.00001f));
+    if (cont && !rej) {
+        const float inv = xrcp(det);
+        const float u = xmul(sh, inv);
+        if (u < 0.0f || u > 1.0f)
+            return;
+        const f3 q = xcross(s, AB);
+        const float v = xmul(xdot(d, q), inv);
+        if (v < 0.0f || xadd(u, v) > 1.0f)
+            return;
+        const float dst = xmul(xdot(AC, q), inv);
+        if (dst < 0.001f)
+            return;
+        if (dst < best) {
+            best = dst;
+            bestId = idx;
+        }
+    }
 }
 
 // general exact closest hit against the shared-memory tables (spheres from global)
@@ -142,10 +182,9 @@ __device__ __noinline__ void closest_exact_smem(const RenderArgs &a, const float
     bestId = -1;
     for (int k = 0; k < nsph; ++k)
         sphere_test_exact(o, d, __ldg(&a.sc.s0[k]), k, best, bestId);
-    unsigned dummy[1];
-#pragma unroll 2
+#pragma unroll 4
     for (int i = 0; i < ntris; ++i)
-        tri_test_exact<false>(o, d, G[3 * i], G[3 * i + 1], G[3 * i + 2], i, best, bestId, dummy);
+        tri_test_exact_sl(o, d, G[3 * i], G[3 * i + 1], G[3 * i + 2], i, best, bestId);
 }
 
 template <int R>
@@ -158,6 +197,7 @@ __global__ void __launch_bounds__(FAST_THREADS) render_fast_kernel(const RenderA
     float4 *sG = sF + 4 * ntris;
     float4 *sState = sG + 3 * ntris;
     float2 *sHit = reinterpret_cast<float2 *>(sState + FAST_THREADS * R);
+    unsigned char *sList = reinterpret_cast<unsigned char *>(sHit + FAST_THREADS * R); // [WARPS][32 * R]
 
     for (int i = threadIdx.x; i < 4 * ntris; i += FAST_THREADS)
         sF[i] = tab[i];
@@ -187,6 +227,7 @@ __global__ void __launch_bounds__(FAST_THREADS) render_fast_kernel(const RenderA
 
     float4 *myState = sState + threadIdx.x; // slot r at myState[r * FAST_THREADS]
     float2 *myHit = sHit + threadIdx.x;
+    unsigned char *myList = sList + warp * 32 * R;
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         uint32_t seed = (uint32_t)(x0 + r * a.col_step + y * a.W) + (uint32_t)g * (uint32_t)(a.W * a.H);
@@ -259,10 +300,8 @@ __global__ void __launch_bounds__(FAST_THREADS) render_fast_kernel(const RenderA
         unsigned hits = 0;
 #pragma unroll
         for (int r = 0; r < R; ++r)
-            if (id[r] != -1 && ((valid >> r) & 1u)) {
+            if (id[r] != -1 && ((valid >> r) & 1u))
                 hits |= 1u << r;
-                myHit[r * FAST_THREADS] = make_float2(best[r], __int_as_float(id[r]));
-            }
         if (s == s0) {
             geom = hits;
             if (a.ids != nullptr && g == a.split_first) {
@@ -272,30 +311,56 @@ __global__ void __launch_bounds__(FAST_THREADS) render_fast_kernel(const RenderA
                         a.ids[(size_t)cj * a.out_w + ci0 + r] = id[r];
             }
         }
-        // ---- paths of the pixels whose primary ray hit (rare): bounce loop with exact sweeps ----
-        while (hits) {
-            const int r = __ffs(hits) - 1;
-            hits &= hits - 1;
-            float4 st = myState[r * FAST_THREADS];
-            const float2 h = myHit[r * FAST_THREADS];
-            Lane L;
-            L.pos = a.origin;
-            L.dir = primary_dir(a, dx_of(r), dy);
-            L.tint = mk3(1.f, 1.f, 1.f);
-            L.light = mk3(0.f, 0.f, 0.f);
-            L.rng = __float_as_uint(st.x);
-            L.bounce = 0;
-            float bst = h.x;
-            int bid = __float_as_int(h.y);
-            while (!shade(L, a, bst, bid)) {
-                closest_exact_smem(a, sG, ntris, nsph, L.pos, L.dir, bst, bid);
-                nrays++;
+        // ---- paths of the pixels whose primary ray hit (rare) ----
+        // The warp pools its hit pixels and hands them out one per lane, so a silhouette tile with a few
+        // hits costs one batch, not one serial path per owner lane.  A worker lane runs the whole path of
+        // "its" pixel in registers; only {rng, acc} and the primary hit travel through shared memory.
+        if (__any_sync(0xffffffffu, hits != 0)) {
+            int n = 0;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const bool mine = (hits >> r) & 1u;
+                const unsigned m = __ballot_sync(0xffffffffu, mine);
+                if (mine) {
+                    const int off = n + __popc(m & ((1u << lane) - 1u));
+                    myList[off] = (unsigned char)(r * 32 + lane);
+                    myHit[r * FAST_THREADS] = make_float2(best[r], __int_as_float(id[r]));
+                }
+                n += __popc(m);
             }
-            st.x = __uint_as_float(L.rng);
-            st.y = xadd(st.y, xmul(L.light.x, w)); // main.c:99
-            st.z = xadd(st.z, xmul(L.light.y, w));
-            st.w = xadd(st.w, xmul(L.light.z, w));
-            myState[r * FAST_THREADS] = st;
+            __syncwarp();
+            for (int b = 0; b < n; b += 32) {
+                const int e = b + lane;
+                if (e < n) {
+                    const int slot = myList[e];
+                    const int ol = slot & 31, r = slot >> 5; // owner lane, its pixel index
+                    const int sidx = r * FAST_THREADS + warp * 32 + ol;
+                    const int px = a.col_start + ((blockIdx.x * FAST_LX + (ol % FAST_LX)) * R + r) * a.col_step;
+                    const int pcj = (blockIdx.y * FAST_WARPS + warp) * FAST_LY + ol / FAST_LX;
+                    const int py = a.row_start + (pcj / a.band_h) * a.row_step + (pcj % a.band_h);
+                    float4 st = sState[sidx];
+                    const float2 h = sHit[sidx];
+                    Lane L;
+                    L.pos = a.origin;
+                    L.dir = primary_dir(a, xdiv((float)(px - a.W / 2), fh), xdiv((float)(py - a.H / 2), fh));
+                    L.tint = mk3(1.f, 1.f, 1.f);
+                    L.light = mk3(0.f, 0.f, 0.f);
+                    L.rng = __float_as_uint(st.x);
+                    L.bounce = 0;
+                    float bst = h.x;
+                    int bid = __float_as_int(h.y);
+                    while (!shade(L, a, bst, bid)) {
+                        closest_exact_smem(a, sG, ntris, nsph, L.pos, L.dir, bst, bid);
+                        nrays++;
+                    }
+                    st.x = __uint_as_float(L.rng);
+                    st.y = xadd(st.y, xmul(L.light.x, w)); // main.c:99
+                    st.z = xadd(st.z, xmul(L.light.y, w));
+                    st.w = xadd(st.w, xmul(L.light.z, w));
+                    sState[sidx] = st;
+                }
+                __syncwarp();
+            }
         }
     }
 
