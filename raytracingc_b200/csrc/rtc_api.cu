@@ -16,6 +16,8 @@
 #include "rtc_b200.h"
 #include "rtc_kernels.cuh"
 #include "rtc_fast.cuh"
+#include "rtc_paths.cuh"
+#include "rtc_sky.cuh"
 
 static_assert(sizeof(Triangle) == 68, "Triangle must match reference raytracing.h:41-45");
 static_assert(sizeof(Sphere) == 36, "Sphere must match reference raytracing.h:34-39");
@@ -67,7 +69,7 @@ void host_cross(const float u[3], const float v[3], float out[3])
 struct RtcScene {
     int device = 0;
     int ntris = 0, nsph = 0;
-    float4 *g0 = nullptr, *g1 = nullptr, *g2 = nullptr, *m0 = nullptr;
+    float4 *geo = nullptr, *m0 = nullptr;
     float *m1 = nullptr;
     float4 *s0 = nullptr, *s1 = nullptr;
     float *s2 = nullptr;
@@ -77,6 +79,10 @@ struct RtcScene {
     float4 *tab = nullptr; // per-frame edge-function table of the primary pre-filter (4 x float4 per triangle)
     int cap_tab = 0;
     int max_smem_optin = 0;
+    int nsm = 0;
+    int *list = nullptr;          // per-frame work list of primary-hit pixels (sky kernel -> path kernel)
+    size_t cap_list = 0;
+    unsigned *counters = nullptr; // [0] list length, [1] path-kernel work cursor
 };
 
 extern "C" {
@@ -137,9 +143,7 @@ void rtc_scene_destroy(RtcScene *sc)
     if (!sc)
         return;
     cudaSetDevice(sc->device);
-    cudaFree(sc->g0);
-    cudaFree(sc->g1);
-    cudaFree(sc->g2);
+    cudaFree(sc->geo);
     cudaFree(sc->m0);
     cudaFree(sc->m1);
     cudaFree(sc->s0);
@@ -147,20 +151,20 @@ void rtc_scene_destroy(RtcScene *sc)
     cudaFree(sc->s2);
     cudaFree(sc->raw);
     cudaFree(sc->tab);
+    cudaFree(sc->list);
+    cudaFree(sc->counters);
     delete sc;
 }
 
 static int scene_reserve(RtcScene *sc, int ntris, int nsph)
 {
     CU(cudaSetDevice(sc->device));
-    if (ntris > sc->cap_tris || !sc->g0) {
+    if (ntris > sc->cap_tris || !sc->geo) {
         size_t nt = ntris > 0 ? ntris : 1;
-        cudaFree(sc->g0); cudaFree(sc->g1); cudaFree(sc->g2); cudaFree(sc->m0); cudaFree(sc->m1);
-        sc->g0 = sc->g1 = sc->g2 = sc->m0 = nullptr;
+        cudaFree(sc->geo); cudaFree(sc->m0); cudaFree(sc->m1);
+        sc->geo = sc->m0 = nullptr;
         sc->m1 = nullptr;
-        CU(cudaMalloc(&sc->g0, sizeof(float4) * nt));
-        CU(cudaMalloc(&sc->g1, sizeof(float4) * nt));
-        CU(cudaMalloc(&sc->g2, sizeof(float4) * nt));
+        CU(cudaMalloc(&sc->geo, sizeof(float4) * 3 * nt));
         CU(cudaMalloc(&sc->m0, sizeof(float4) * nt));
         CU(cudaMalloc(&sc->m1, sizeof(float) * nt));
         sc->cap_tris = (int)nt;
@@ -204,7 +208,7 @@ static int scene_upload(RtcScene *sc, const Triangle *tris, int ntris, const Sph
     }
     if (ntris > 0) {
         CU(cudaMemcpyAsync(raw_t, tris, sizeof(Triangle) * (size_t)ntris, cudaMemcpyHostToDevice, st));
-        rtc::flatten_kernel<<<(ntris + 127) / 128, 128, 0, st>>>(raw_t, ntris, sc->g0, sc->g1, sc->g2, sc->m0, sc->m1);
+        rtc::flatten_kernel<<<(ntris + 127) / 128, 128, 0, st>>>(raw_t, ntris, sc->geo, sc->m0, sc->m1);
         CU(cudaGetLastError());
     }
     return RTC_OK;
@@ -265,7 +269,7 @@ rtc::RenderArgs make_args(const RtcScene *sc, const Scene *sky, const Camera *ca
 {
     rtc::RenderArgs a;
     memset(&a, 0, sizeof a);
-    a.sc.g0 = sc->g0; a.sc.g1 = sc->g1; a.sc.g2 = sc->g2; a.sc.m0 = sc->m0; a.sc.m1 = sc->m1;
+    a.sc.geo = sc->geo; a.sc.m0 = sc->m0; a.sc.m1 = sc->m1;
     a.sc.ntris = sc->ntris;
     a.sc.s0 = sc->s0; a.sc.s1 = sc->s1; a.sc.s2 = sc->s2;
     a.sc.nsph = sc->nsph;
@@ -318,33 +322,88 @@ bool camera_is_orthonormal(const Camera *c)
            std::isfinite(c->origin.z);
 }
 
-// pixels per lane of the fast kernel, 0 = use the exact kernel
+// env override helpers (test / tuning knobs; unset in production)
+int env_int(const char *name, int dflt)
+{
+    const char *e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
+
+// pixels per lane of the sky kernel, 0 = the filtered path is not applicable (exact kernels only)
 int fast_path_R(const RtcScene *sc, const Camera *cam, const RtcDeviceJob *job)
 {
-    if (job->flags & (RTC_FLAG_EXACT_ONLY | RTC_FLAG_COUNT_EXITS))
+    (void)sc;
+    if (job->flags & (RTC_FLAG_EXACT_ONLY | RTC_FLAG_COUNT_EXITS | RTC_FLAG_PATHS_ONLY))
         return 0;
     if (job->maxBounce < 1 || !camera_is_orthonormal(cam))
         return 0;
     if ((long long)job->width * job->height >= (1ll << 31))
         return 0;
-    int R = 0;
+    int G = job->nsplit > 1 ? job->nsplit : 1;
+    if (job->spp < G)
+        return 0; // some sub-stream has no samples: no classification sample to hang the work list on
     const char *e = getenv("RTC_FAST_R");
-    if (e)
-        R = atoi(e);
+    int R = e ? atoi(e) : -1;
     if (e && R == 0)
         return 0;
-    if (R != 1 && R != 2 && R != 4 && R != 8) {
+    if (R != 1 && R != 2 && R != 4 && R != 8 && R != 16) {
         long long px = (long long)job->out_w * job->out_h;
         R = px >= 4000000 ? 8 : (px >= 1000000 ? 4 : 2);
     }
-    int optin = sc->max_smem_optin;
-    if (optin == 0) {
-        cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, sc->device);
-        const_cast<RtcScene *>(sc)->max_smem_optin = optin;
+    return R;
+}
+
+int ensure_scratch(RtcScene *sc, size_t npix)
+{
+    if (!sc->counters)
+        CU(cudaMalloc(&sc->counters, 4 * sizeof(unsigned)));
+    if (npix > sc->cap_list || !sc->list) {
+        cudaFree(sc->list);
+        sc->list = nullptr;
+        CU(cudaMalloc(&sc->list, sizeof(int) * (npix ? npix : 1)));
+        sc->cap_list = npix;
     }
-    while (R >= 1 && rtc::fast_smem_bytes(sc->ntris, R) > (size_t)optin)
-        R >>= 1;
-    return R; // 0 when even R = 1 does not fit: the scene is too large for the resident-table kernel
+    if (!sc->nsm) {
+        CU(cudaDeviceGetAttribute(&sc->nsm, cudaDevAttrMultiProcessorCount, sc->device));
+        CU(cudaDeviceGetAttribute(&sc->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, sc->device));
+    }
+    return RTC_OK;
+}
+
+// the path kernel: persistent grid over a work list (list == nullptr: every pixel of the subset)
+int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, int planes, int write_ids, cudaStream_t st)
+{
+    rtc::PathWork w;
+    w.list = list;
+    w.list_count = sc->counters;
+    w.cursor = sc->counters + 1;
+    w.planes = planes;
+    w.write_ids = write_ids;
+    w.tile = env_int("RTC_PATH_TILE", rtc::PATH_TILE);
+    if (w.tile < 1 || w.tile > rtc::PATH_TILE)
+        w.tile = rtc::PATH_TILE;
+    const size_t resident = rtc::path_smem_bytes(sc->ntris, false);
+    const bool stream = env_int("RTC_FORCE_STREAM", 0) != 0 || resident > 96 * 1024;
+    const size_t smem = rtc::path_smem_bytes(sc->ntris, stream);
+    int per_sm = 0;
+    if (stream) {
+        CU(cudaFuncSetAttribute(rtc::render_paths_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rtc::render_paths_kernel<true>, rtc::PATH_THREADS, smem));
+    } else {
+        CU(cudaFuncSetAttribute(rtc::render_paths_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rtc::render_paths_kernel<false>, rtc::PATH_THREADS, smem));
+    }
+    if (per_sm < 1)
+        return fail(RTC_ERR_CUDA, "path kernel does not fit on an SM (smem %zu)", smem);
+    long long tasks = (long long)a.out_w * a.out_h * planes; // upper bound when a list is used
+    long long want = (tasks + rtc::PATH_THREADS - 1) / rtc::PATH_THREADS;
+    int blocks = (int)std::min<long long>((long long)sc->nsm * per_sm, want > 0 ? want : 1);
+    if (stream)
+        rtc::render_paths_kernel<true><<<blocks, rtc::PATH_THREADS, smem, st>>>(a, w);
+    else
+        rtc::render_paths_kernel<false><<<blocks, rtc::PATH_THREADS, smem, st>>>(a, w);
+    CU(cudaGetLastError());
+    return RTC_OK;
 }
 
 rtc::PrimaryFrame make_primary_frame(const Camera *cam, const RtcDeviceJob *job, int R)
@@ -393,7 +452,7 @@ int rtc_render_launch_count(const RtcScene *sc, const RtcDeviceJob *job, int wan
     (void)want_ids;
     if (!job || job->out_w <= 0 || job->out_h <= 0)
         return 0;
-    return 1; // the fused render kernel; ids come from its first sweep
+    return 3; // prepare_primary + sky kernel + path kernel (exact-only modes launch 1)
 }
 
 int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, const RtcDeviceJob *job,
@@ -418,8 +477,13 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
     a.stats = reinterpret_cast<unsigned long long *>(d_stats);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     int R = fast_path_R(sc, cam, job);
+    RtcScene *msc = const_cast<RtcScene *>(sc); // per-frame tables and work lists are scratch owned by the handle
+    if (R > 0 || (job->flags & RTC_FLAG_PATHS_ONLY)) {
+        if ((rc = ensure_scratch(msc, (size_t)job->out_w * job->out_h)))
+            return rc;
+        CU(cudaMemsetAsync(msc->counters, 0, 4 * sizeof(unsigned), st));
+    }
     if (R > 0) {
-        RtcScene *msc = const_cast<RtcScene *>(sc); // the per-frame table is scratch owned by the handle
         if (sc->ntris > msc->cap_tab || !msc->tab) {
             cudaFree(msc->tab);
             msc->tab = nullptr;
@@ -431,26 +495,40 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
             rtc::prepare_primary_kernel<<<(sc->ntris + 127) / 128, 128, 0, st>>>(a.sc, fr, msc->tab);
             CU(cudaGetLastError());
         }
-        size_t smem = rtc::fast_smem_bytes(sc->ntris, R);
+        rtc::SkyWork sw;
+        sw.list = msc->list;
+        sw.list_count = msc->counters;
+        sw.tile = env_int("RTC_SKY_TILE", rtc::SKY_TILE);
+        if (sw.tile < 1 || sw.tile > rtc::SKY_TILE)
+            sw.tile = rtc::SKY_TILE;
+        sw.stream = (env_int("RTC_FORCE_STREAM", 0) != 0 || sc->ntris > rtc::SKY_TILE) ? 1 : 0;
+        size_t smem = rtc::sky_smem_bytes(sc->ntris, sw.stream != 0);
         dim3 fgrid((job->out_w + rtc::FAST_LX * R - 1) / (rtc::FAST_LX * R),
                    (job->out_h + rtc::FAST_LY * rtc::FAST_WARPS - 1) / (rtc::FAST_LY * rtc::FAST_WARPS), planes);
-#define LAUNCH_FAST(RR)                                                                                         \
+#define LAUNCH_SKY(RR)                                                                                          \
     do {                                                                                                        \
-        CU(cudaFuncSetAttribute(rtc::render_fast_kernel<RR>, cudaFuncAttributeMaxDynamicSharedMemorySize,        \
+        CU(cudaFuncSetAttribute(rtc::render_sky_kernel<RR>, cudaFuncAttributeMaxDynamicSharedMemorySize,         \
                                 (int)smem));                                                                    \
-        rtc::render_fast_kernel<RR><<<fgrid, rtc::FAST_THREADS, smem, st>>>(a, msc->tab);                        \
+        rtc::render_sky_kernel<RR><<<fgrid, rtc::FAST_THREADS, smem, st>>>(a, msc->tab, sw);                     \
     } while (0)
-        if (R == 8)
-            LAUNCH_FAST(8);
+        if (R == 16)
+            LAUNCH_SKY(16);
+        else if (R == 8)
+            LAUNCH_SKY(8);
         else if (R == 4)
-            LAUNCH_FAST(4);
+            LAUNCH_SKY(4);
         else if (R == 2)
-            LAUNCH_FAST(2);
+            LAUNCH_SKY(2);
         else
-            LAUNCH_FAST(1);
-#undef LAUNCH_FAST
+            LAUNCH_SKY(1);
+#undef LAUNCH_SKY
         CU(cudaGetLastError());
-        return RTC_OK;
+        return launch_paths(msc, a, msc->list, planes, 0, st);
+    }
+    if (job->flags & RTC_FLAG_PATHS_ONLY) {
+        if (job->maxBounce < 1)
+            return fail(RTC_ERR_ARG, "RTC_FLAG_PATHS_ONLY needs maxBounce >= 1");
+        return launch_paths(msc, a, nullptr, planes, 1, st);
     }
     dim3 grid((job->out_w + rtc::CTA_W - 1) / rtc::CTA_W, (job->out_h + rtc::CTA_H - 1) / rtc::CTA_H, planes);
     if (job->flags & RTC_FLAG_COUNT_EXITS)

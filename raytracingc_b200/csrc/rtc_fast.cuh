@@ -39,7 +39,7 @@ __global__ void prepare_primary_kernel(const DeviceScene sc, const PrimaryFrame 
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= sc.ntris)
         return;
-    const float4 p0 = sc.g0[i], p1 = sc.g1[i], p2 = sc.g2[i];
+    const float4 p0 = sc.geo[3 * i], p1 = sc.geo[3 * i + 1], p2 = sc.geo[3 * i + 2];
     const f3 A = mk3(p0.x, p0.y, p0.z), AB = mk3(p1.x, p1.y, p1.z), AC = mk3(p2.x, p2.y, p2.z);
     const f3 n = mk3(p0.w, p1.w, p2.w);
     // exactly the reference's float values for a primary ray: s, q = s x AB, tq = AC . q
@@ -201,11 +201,8 @@ __global__ void __launch_bounds__(FAST_THREADS) render_fast_kernel(const RenderA
 
     for (int i = threadIdx.x; i < 4 * ntris; i += FAST_THREADS)
         sF[i] = tab[i];
-    for (int i = threadIdx.x; i < ntris; i += FAST_THREADS) {
-        sG[3 * i] = a.sc.g0[i];
-        sG[3 * i + 1] = a.sc.g1[i];
-        sG[3 * i + 2] = a.sc.g2[i];
-    }
+    for (int i = threadIdx.x; i < 3 * ntris; i += FAST_THREADS)
+        sG[i] = a.sc.geo[i];
     __syncthreads();
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;

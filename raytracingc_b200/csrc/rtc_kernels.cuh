@@ -25,8 +25,7 @@ constexpr int CTA_W = TILE_W * CTA_WARPS_X, CTA_H = TILE_H * CTA_WARPS_Y;
 
 // ---- flatten ------------------------------------------------------------------
 // One thread per triangle; raw is the caller's Triangle[] viewed as floats (17 per record).
-__global__ void flatten_kernel(const float *__restrict__ raw, int n, float4 *g0, float4 *g1, float4 *g2, float4 *m0,
-                               float *m1)
+__global__ void flatten_kernel(const float *__restrict__ raw, int n, float4 *geo, float4 *m0, float *m1)
 {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n)
@@ -34,9 +33,9 @@ __global__ void flatten_kernel(const float *__restrict__ raw, int n, float4 *g0,
     const float *t = raw + (size_t)i * 17;
     f3 A = mk3(t[0], t[1], t[2]), B = mk3(t[3], t[4], t[5]), C = mk3(t[6], t[7], t[8]);
     f3 AB = xsub3(B, A), AC = xsub3(C, A); // reference raytracing.c:191-192
-    g0[i] = make_float4(A.x, A.y, A.z, t[9]);
-    g1[i] = make_float4(AB.x, AB.y, AB.z, t[10]);
-    g2[i] = make_float4(AC.x, AC.y, AC.z, t[11]);
+    geo[3 * i] = make_float4(A.x, A.y, A.z, t[9]);
+    geo[3 * i + 1] = make_float4(AB.x, AB.y, AB.z, t[10]);
+    geo[3 * i + 2] = make_float4(AC.x, AC.y, AC.z, t[11]);
     m0[i] = make_float4(t[12], t[13], t[14], t[15]);
     m1[i] = t[16];
 }
@@ -144,7 +143,7 @@ __device__ __forceinline__ bool shade(Lane &L, const RenderArgs &a, float best, 
     float4 m0;
     float smooth;
     if (bestId >= 0) {
-        n = mk3(__ldg(&a.sc.g0[bestId]).w, __ldg(&a.sc.g1[bestId]).w, __ldg(&a.sc.g2[bestId]).w);
+        n = mk3(__ldg(&a.sc.geo[3 * bestId]).w, __ldg(&a.sc.geo[3 * bestId + 1]).w, __ldg(&a.sc.geo[3 * bestId + 2]).w);
         m0 = __ldg(&a.sc.m0[bestId]);
         smooth = __ldg(&a.sc.m1[bestId]);
     } else {
@@ -216,7 +215,7 @@ __global__ void __launch_bounds__(CTA_THREADS) render_kernel(const RenderArgs a)
         for (int k = 0; k < nsph; ++k)
             sphere_test_exact(L.pos, L.dir, __ldg(&a.sc.s0[k]), k, best, id);
         for (int i = 0; i < ntris; ++i)
-            tri_test_exact<false>(L.pos, L.dir, __ldg(&a.sc.g0[i]), __ldg(&a.sc.g1[i]), __ldg(&a.sc.g2[i]), i, best,
+            tri_test_exact<false>(L.pos, L.dir, __ldg(&a.sc.geo[3 * i]), __ldg(&a.sc.geo[3 * i + 1]), __ldg(&a.sc.geo[3 * i + 2]), i, best,
                                   id, exits);
         firstId = id;
     }
@@ -230,7 +229,7 @@ __global__ void __launch_bounds__(CTA_THREADS) render_kernel(const RenderArgs a)
                 sphere_test_exact(L.pos, L.dir, __ldg(&a.sc.s0[k]), k, best, bestId);
 #pragma unroll 2
             for (int i = 0; i < ntris; ++i)
-                tri_test_exact<COUNT>(L.pos, L.dir, __ldg(&a.sc.g0[i]), __ldg(&a.sc.g1[i]), __ldg(&a.sc.g2[i]), i,
+                tri_test_exact<COUNT>(L.pos, L.dir, __ldg(&a.sc.geo[3 * i]), __ldg(&a.sc.geo[3 * i + 1]), __ldg(&a.sc.geo[3 * i + 2]), i,
                                       best, bestId, exits);
             nrays++;
             if (first) {

@@ -1,0 +1,261 @@
+// rtc_paths.cuh -- the path kernel: one lane = one pixel's RNG stream, exact arithmetic for every ray.
+//
+// A lane is a state machine over (sample, bounce) of "its" pixel (the stream is serial per pixel: seeded once,
+// main.c:95, continuing across samples, main.c:98-99).  The warp iterates
+//     sweep the lane's current ray over ALL triangles (calculateRayCollision, raytracing.c:216-240)  ->  shade
+// so lanes with different path lengths never wait for each other, and a lane whose pixel is finished fetches
+// the next pixel from a global work list (persistent lanes: no tail beyond one pixel's own serial chain).
+//
+// Work list: either the compact list of primary-hit pixels produced by the sky kernel (rtc_sky.cuh), or, with
+// list == nullptr, every pixel of the subset.  A task is (pixel, plane); plane = sub-stream of a sample split.
+//
+// Geometry (48 B per triangle, rtc_scene.cuh) lives in shared memory:
+//   STREAM = false  the whole scene is resident (loaded once per CTA); warps run independently.
+//   STREAM = true   scenes of any size: PATH_TILE-triangle tiles are streamed by the TMA unit
+//                   (cp.async.bulk + mbarrier, double-buffered); the CTA's warps sweep in lock-step.
+#pragma once
+
+#include "rtc_kernels.cuh"
+#include "rtc_tma.cuh"
+
+namespace rtc {
+
+constexpr int PATH_THREADS = 128;
+constexpr int PATH_TILE = 1024; // triangles per streamed tile: 48 KB per stage, 2 stages
+
+struct PathWork {
+    const int *list;            // compact pixel indices (cj * out_w + ci) or nullptr = all pixels
+    const unsigned *list_count; // device counter written by the sky kernel (used when list != nullptr)
+    unsigned *cursor;           // device work cursor, zeroed before the launch
+    int planes;                 // sub-streams rendered by this launch
+    int write_ids;              // 1: this kernel owns the primary-id map (no sky kernel ran)
+    int tile;                   // triangles per streamed tile (<= PATH_TILE), STREAM only
+};
+
+__host__ __device__ inline size_t path_smem_bytes(int ntris, bool stream)
+{
+    return stream ? (size_t)2 * PATH_TILE * 3 * sizeof(float4) : (size_t)(ntris > 0 ? ntris : 1) * 3 * sizeof(float4);
+}
+
+// The reference's ray-triangle test arranged for SIMT (same operations, same order, same decisions): the values
+// up to s.h are computed straight-line for every pair -- independent work across unrolled triangles -- and the
+// exits are taken on those exact values.  Two exits are decided without the division:
+//   * sign(s.h) != sign(det), |s.h| >= 1e-30, |det| <= 2^20  =>  u = fl(s.h * fl(1/det)) < 0   (cannot round to -0)
+//   * same sign and |s.h| > |det| * 1.00001                     =>  u > 1                       (margin >> 3 roundings)
+// Every other pair continues with the reference's remaining operations.
+__device__ __forceinline__ void tri_test_sl(const f3 &o, const f3 &d, const float4 &p0, const float4 &p1,
+                                            const float4 &p2, int idx, float &best, int &bestId)
+{
+    const f3 n = mk3(p0.w, p1.w, p2.w);
+    const f3 AB = mk3(p1.x, p1.y, p1.z), AC = mk3(p2.x, p2.y, p2.z);
+    const float c = xdot(d, n);
+    const f3 h = xcross(d, AC);
+    const float det = xdot(AB, h);
+    const f3 s = xsub3(o, mk3(p0.x, p0.y, p0.z));
+    const float sh = xdot(s, h);
+    const bool cont = !(c >= 0.0f) && !(fabsf(det) < 0.001f); // -EPS < det < EPS  <=>  |det| < EPS
+    const float adet = fabsf(det), ash = fabsf(sh);
+    const bool opp = (__float_as_int(sh) ^ __float_as_int(det)) < 0;
+    const bool rej = opp ? (ash >= 1e-30f && adet <= 1048576.0f) : (ash > xmul(adet, 1.00001f));
+    if (cont && !rej) {
+        const float inv = xrcp(det);
+        const float u = xmul(sh, inv);
+        if (u < 0.0f || u > 1.0f)
+            return;
+        const f3 q = xcross(s, AB);
+        const float v = xmul(xdot(d, q), inv);
+        if (v < 0.0f || xadd(u, v) > 1.0f)
+            return;
+        const float dst = xmul(xdot(AC, q), inv);
+        if (dst < 0.001f)
+            return;
+        if (dst < best) { // strict <: first index wins ties (raytracing.c:232)
+            best = dst;
+            bestId = idx;
+        }
+    }
+}
+
+template <bool STREAM>
+__global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const RenderArgs a, const PathWork w)
+{
+    extern __shared__ float4 sGeo[];
+    __shared__ uint64_t bars[2];
+    const int ntris = a.sc.ntris;
+    const int nsph = a.trianglesOnly ? 0 : a.sc.nsph;
+    const int lane = threadIdx.x & 31;
+    const int tile = w.tile;
+    const int ntiles = STREAM ? (ntris + tile - 1) / tile : 1;
+
+    if (!STREAM) {
+        for (int i = threadIdx.x; i < 3 * ntris; i += PATH_THREADS)
+            sGeo[i] = a.sc.geo[i];
+    } else if (threadIdx.x == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        fence_barrier_init();
+    }
+    __syncthreads();
+
+    const unsigned npix = w.list ? *w.list_count : (unsigned)(a.out_w * a.out_h);
+    const unsigned total = npix * (unsigned)w.planes;
+    const float fh = (float)(a.H / 2);
+    const float wgt = (float)(1.0 / (double)a.spp); // main.c:99
+
+    Lane L;
+    f3 pdir = mk3(0.f, 0.f, 0.f);
+    int pix = 0, plane = 0, s_end = 0;
+    bool active = false, exhausted = false, first = false;
+    unsigned long long nrays = 0, nhitpix = 0;
+    uint32_t k0 = 0; // tiles consumed so far (STREAM): stage = k & 1, parity = (k >> 1) & 1
+
+    auto issue = [&](uint32_t k, int t) {
+        const int n = min(tile, ntris - t * tile);
+        const uint32_t bytes = (uint32_t)n * 3u * (uint32_t)sizeof(float4);
+        fence_proxy_async();
+        mbar_arrive_expect_tx(&bars[k & 1], bytes);
+        tma_load_1d(sGeo + (size_t)(k & 1) * PATH_TILE * 3, a.sc.geo + (size_t)t * tile * 3, bytes, &bars[k & 1]);
+    };
+
+    while (true) {
+        // ---- idle lanes fetch the next (pixel, plane) task ----
+        {
+            const bool need = !active && !exhausted;
+            const unsigned m = __ballot_sync(0xffffffffu, need);
+            if (m) {
+                unsigned base = 0;
+                const int leader = __ffs(m) - 1;
+                if (lane == leader)
+                    base = atomicAdd(w.cursor, (unsigned)__popc(m));
+                base = __shfl_sync(0xffffffffu, base, leader);
+                if (need) {
+                    const unsigned t = base + __popc(m & ((1u << lane) - 1u));
+                    if (t < total) {
+                        plane = (int)(t / npix);
+                        pix = w.list ? w.list[t % npix] : (int)(t % npix);
+                        const int ci = pix % a.out_w, cj = pix / a.out_w;
+                        const int x = a.col_start + ci * a.col_step;
+                        const int y = a.row_start + (cj / a.band_h) * a.row_step + (cj % a.band_h);
+                        const int g = a.split_first + plane;
+                        const float dx = xdiv((float)(x - a.W / 2), fh), dy = xdiv((float)(y - a.H / 2), fh);
+                        pdir = xnormalize(xadd3(xadd3(xscale3(a.ex, dx), xscale3(a.ey, dy)), xscale3(a.ez, a.fov)));
+                        L.pos = a.origin;
+                        L.dir = pdir;
+                        L.tint = mk3(1.f, 1.f, 1.f);
+                        L.light = mk3(0.f, 0.f, 0.f);
+                        L.acc = mk3(0.f, 0.f, 0.f);
+                        L.rng = (uint32_t)(x + y * a.W) + (uint32_t)g * (uint32_t)(a.W * a.H); // main.c:95
+                        L.sample = (int)((long long)g * a.spp / a.nsplit);
+                        s_end = (int)((long long)(g + 1) * a.spp / a.nsplit);
+                        L.bounce = 0;
+                        first = true;
+                        active = L.sample < s_end;
+                        if (!active) { // empty sample range: the pixel's partial sum is zero
+                            if (a.accum != nullptr) {
+                                float *p = a.accum + ((size_t)plane * a.out_w * a.out_h + pix) * 3;
+                                p[0] = p[1] = p[2] = 0.f;
+                            }
+                        }
+                    } else {
+                        exhausted = true;
+                    }
+                }
+            }
+        }
+        const bool any = STREAM ? (__syncthreads_or(active) != 0) : __any_sync(0xffffffffu, active);
+        if (!any)
+            break;
+
+        // ---- closest hit of the lane's current ray: spheres first, then triangles in order ----
+        float best = 999999.0f;
+        int bestId = -1;
+        if (active)
+            for (int k = 0; k < nsph; ++k)
+                sphere_test_exact(L.pos, L.dir, __ldg(&a.sc.s0[k]), k, best, bestId);
+        if (!STREAM) {
+            if (active) {
+#pragma unroll 4
+                for (int i = 0; i < ntris; ++i)
+                    tri_test_sl(L.pos, L.dir, sGeo[3 * i], sGeo[3 * i + 1], sGeo[3 * i + 2], i, best, bestId);
+            }
+        } else {
+            if (threadIdx.x == 0) {
+                issue(k0, 0);
+                if (ntiles > 1)
+                    issue(k0 + 1, 1);
+            }
+            for (int t = 0; t < ntiles; ++t) {
+                const uint32_t k = k0 + (uint32_t)t;
+                mbar_wait(&bars[k & 1], (k >> 1) & 1u);
+                if (active) {
+                    const float4 *S = sGeo + (size_t)(k & 1) * PATH_TILE * 3;
+                    const int n = min(tile, ntris - t * tile), base = t * tile;
+#pragma unroll 4
+                    for (int i = 0; i < n; ++i)
+                        tri_test_sl(L.pos, L.dir, S[3 * i], S[3 * i + 1], S[3 * i + 2], base + i, best, bestId);
+                }
+                __syncthreads(); // every warp is done with this stage
+                if (threadIdx.x == 0 && t + 2 < ntiles)
+                    issue(k + 2, t + 2);
+            }
+            k0 += (uint32_t)ntiles;
+        }
+
+        // ---- shade (calcColor's loop body), advance the state machine ----
+        if (active) {
+            nrays++;
+            if (first) {
+                first = false;
+                if (w.write_ids && plane == 0) {
+                    if (a.ids != nullptr)
+                        a.ids[pix] = bestId;
+                    nhitpix += bestId != -1;
+                }
+            }
+            if (shade(L, a, best, bestId)) {
+                L.acc = xadd3(L.acc, xscale3(L.light, wgt)); // main.c:99
+                L.sample++;
+                if (L.sample >= s_end) {
+                    active = false;
+                    if (a.accum != nullptr) {
+                        float *p = a.accum + ((size_t)plane * a.out_w * a.out_h + pix) * 3;
+                        p[0] = L.acc.x;
+                        p[1] = L.acc.y;
+                        p[2] = L.acc.z;
+                    }
+                    if (a.rgb != nullptr && a.nsplit == 1) { // vec3ToColor, raytracing.c:11-15
+                        uint8_t *p = a.rgb + (size_t)pix * 3;
+                        p[0] = (uint8_t)float_to_uint8(L.acc.x);
+                        p[1] = (uint8_t)float_to_uint8(L.acc.y);
+                        p[2] = (uint8_t)float_to_uint8(L.acc.z);
+                    }
+                } else {
+                    L.pos = a.origin;
+                    L.dir = pdir;
+                    L.tint = mk3(1.f, 1.f, 1.f);
+                    L.light = mk3(0.f, 0.f, 0.f);
+                    L.bounce = 0;
+                }
+            }
+        }
+    }
+
+    if (a.stats != nullptr) {
+        unsigned long long r = nrays, hp = nhitpix;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            r += __shfl_xor_sync(0xffffffffu, r, o);
+            hp += __shfl_xor_sync(0xffffffffu, hp, o);
+        }
+        if (lane == 0 && r) {
+            atomicAdd(&a.stats[ST_RAYS], r);
+            atomicAdd(&a.stats[ST_TRI_PAIRS], r * (unsigned long long)ntris);
+            atomicAdd(&a.stats[ST_SPH_PAIRS], r * (unsigned long long)nsph);
+            atomicAdd(&a.stats[ST_SLOW_PAIRS], r * (unsigned long long)ntris);
+            if (w.write_ids && a.ids != nullptr)
+                atomicAdd(&a.stats[ST_HIT_PIXELS], hp);
+        }
+    }
+}
+
+} // namespace rtc

@@ -10,17 +10,18 @@ namespace rtc {
 
 // Flattened scene (one per device).  The reference keeps Triangle[] as a 68-byte
 // array of structs and copies each one by value per test (raytracing.c:231);
-// here geometry is structure-of-arrays in three 16-byte-aligned planes so one
-// warp-uniform 128-bit load brings a third of a triangle:
-//     g0[i] = { A.x,  A.y,  A.z,  n.x }
-//     g1[i] = { AB.x, AB.y, AB.z, n.y }      AB = B - A   (raytracing.c:191, hoisted:
-//     g2[i] = { AC.x, AC.y, AC.z, n.z }      AC = C - A    the same float subtraction)
+// here geometry is three 16-byte-aligned float4 per triangle, contiguous (48 B), so one
+// warp-uniform 128-bit load brings a third of a triangle and a tile of triangles is ONE
+// contiguous range for a bulk (TMA) copy into shared memory:
+//     geo[3i+0] = { A.x,  A.y,  A.z,  n.x }
+//     geo[3i+1] = { AB.x, AB.y, AB.z, n.y }      AB = B - A   (raytracing.c:191, hoisted:
+//     geo[3i+2] = { AC.x, AC.y, AC.z, n.z }      AC = C - A    the same float subtraction)
 // 48 B of geometry per triangle are read per (CTA sweep, triangle); the
 // material (20 B in the reference) is read once per closest hit:
 //     m0[i] = { color.r, color.g, color.b, emissionStrength }    m1[i] = smoothness
 // Spheres: s0[k] = { centre.xyz, r }, s1[k] = { color, emission }, s2[k] = smoothness.
 struct DeviceScene {
-    const float4 *g0, *g1, *g2;
+    const float4 *geo;
     const float4 *m0;
     const float *m1;
     int ntris;
@@ -48,6 +49,6 @@ struct RenderArgs {
 };
 
 // stats words
-enum { ST_RAYS = 0, ST_TRI_PAIRS = 1, ST_SPH_PAIRS = 2, ST_EXIT0 = 3, /* ..8 */ ST_HIT_PIXELS = 9, ST_SLOW_PAIRS = 10 };
+enum { ST_RAYS = 0, ST_TRI_PAIRS = 1, ST_SPH_PAIRS = 2, ST_EXIT0 = 3, /* ..8 */ ST_HIT_PIXELS = 9, ST_SLOW_PAIRS = 10, ST_MISMATCH = 11 };
 
 } // namespace rtc
