@@ -42,6 +42,8 @@ extern "C" {
 #define RTC_FLAG_EXACT_ONLY 2u  /* disable the conservative FMA pre-filter: every
                                    ray-triangle pair runs the reference's own
                                    operation sequence (validation mode)          */
+#define RTC_FLAG_PER_PAIR_FILTER 8u /* primary pre-filter evaluated per (pixel, triangle) pair instead of
+                                      per (8x4 pixel block, triangle) + expansion of surviving blocks */
 #define RTC_FLAG_PATHS_ONLY 4u  /* no primary pre-filter: every pixel goes through the
                                    path kernel (exact arithmetic, shared-memory tiles) */
 

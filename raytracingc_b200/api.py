@@ -25,7 +25,7 @@ SPHERE_DTYPE = np.dtype(
     [("pos", "<f4", 3), ("r", "<f4"), ("color", "<f4", 3), ("emissionStrength", "<f4"), ("smoothness", "<f4")])
 
 RTC_SPLIT_TILES, RTC_SPLIT_SAMPLES = 0, 1
-RTC_FLAG_COUNT_EXITS, RTC_FLAG_EXACT_ONLY, RTC_FLAG_PATHS_ONLY = 1, 2, 4
+RTC_FLAG_COUNT_EXITS, RTC_FLAG_EXACT_ONLY, RTC_FLAG_PATHS_ONLY, RTC_FLAG_PER_PAIR_FILTER = 1, 2, 4, 8
 STATS_WORDS = 16
 ERRORS = {1: "RTC_ERR_ARG", 2: "RTC_ERR_NO_GPU", 3: "RTC_ERR_CUDA", 4: "RTC_ERR_NCCL", 5: "RTC_ERR_NOMEM"}
 

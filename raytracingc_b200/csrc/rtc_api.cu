@@ -18,6 +18,7 @@
 #include "rtc_fast.cuh"
 #include "rtc_paths.cuh"
 #include "rtc_sky.cuh"
+#include "rtc_skyblock.cuh"
 
 static_assert(sizeof(Triangle) == 68, "Triangle must match reference raytracing.h:41-45");
 static_assert(sizeof(Sphere) == 36, "Sphere must match reference raytracing.h:34-39");
@@ -406,7 +407,7 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, int pl
     return RTC_OK;
 }
 
-rtc::PrimaryFrame make_primary_frame(const Camera *cam, const RtcDeviceJob *job, int R)
+rtc::PrimaryFrame make_primary_frame(const Camera *cam, const RtcDeviceJob *job, int R, bool block)
 {
     rtc::PrimaryFrame fr;
     fr.origin = to3(cam->origin);
@@ -420,6 +421,21 @@ rtc::PrimaryFrame make_primary_frame(const Camera *cam, const RtcDeviceJob *job,
                  dyhi = (H - 1 - H / 2) / h2;
     fr.dxmax = fmax(fabs(dxlo), fabs(dxhi));
     fr.dymax = fmax(fabs(dylo), fabs(dyhi));
+    fr.block = block ? 1 : 0;
+    fr.hw = fr.hh = 0;
+    if (block) {
+        // half extents of an 8 x 4 pixel block in (dx, dy); inflated for the rounding of the block centre
+        const int cs0 = job->subset.col_step > 0 ? job->subset.col_step : 1;
+        const int bh = job->subset.band_h > 0 ? job->subset.band_h : 1;
+        const int rs0 = bh == 1 ? (job->subset.row_step > 0 ? job->subset.row_step : 1) : 1;
+        fr.hw = 0.5 * (rtc::BLK_W - 1) * cs0 / h2;
+        fr.hh = 0.5 * (rtc::BLK_H - 1) * rs0 / h2;
+        // blocks that stick out of the image have their centre up to one block beyond the last pixel
+        fr.dxmax += 2.0 * fr.hw + 1.0 / h2;
+        fr.dymax += 2.0 * fr.hh + 1.0 / h2;
+        fr.hw = fr.hw * 1.001 + 4e-7 * (fr.dxmax + 1.0);
+        fr.hh = fr.hh * 1.001 + 4e-7 * (fr.dymax + 1.0);
+    }
     double dmax = 0;
     for (double dx : {dxlo, dxhi})
         for (double dy : {dylo, dyhi}) {
@@ -431,7 +447,7 @@ rtc::PrimaryFrame make_primary_frame(const Camera *cam, const RtcDeviceJob *job,
     fr.Dmax = dmax * 1.001; // |D|^2 is convex in (dx, dy): the maximum over the image is at a corner
     int cs = job->subset.col_step > 0 ? job->subset.col_step : 1;
     fr.xstep = cs / h2;
-    fr.max_steps = R - 1;
+    fr.max_steps = block ? 0 : R - 1;
     return fr;
 }
 
@@ -490,7 +506,11 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
             CU(cudaMalloc(&msc->tab, sizeof(float4) * 4 * (size_t)(sc->ntris > 0 ? sc->ntris : 1)));
             msc->cap_tab = sc->ntris > 0 ? sc->ntris : 1;
         }
-        rtc::PrimaryFrame fr = make_primary_frame(cam, job, R);
+        const int nsph_eff = job->trianglesOnly ? 0 : sc->nsph;
+        const int bh_ = job->subset.band_h > 0 ? job->subset.band_h : 1;
+        const bool block = nsph_eff == 0 && !(job->flags & RTC_FLAG_PER_PAIR_FILTER) &&
+                           (bh_ == 1 || bh_ % rtc::BLK_H == 0) && env_int("RTC_SKY_BLOCK", 1) != 0;
+        rtc::PrimaryFrame fr = make_primary_frame(cam, job, R, block);
         if (sc->ntris > 0) {
             rtc::prepare_primary_kernel<<<(sc->ntris + 127) / 128, 128, 0, st>>>(a.sc, fr, msc->tab);
             CU(cudaGetLastError());
@@ -502,6 +522,16 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
         if (sw.tile < 1 || sw.tile > rtc::SKY_TILE)
             sw.tile = rtc::SKY_TILE;
         sw.stream = (env_int("RTC_FORCE_STREAM", 0) != 0 || sc->ntris > rtc::SKY_TILE) ? 1 : 0;
+        if (block) {
+            size_t bsmem = rtc::skyblock_smem_bytes(sc->ntris, sw.stream != 0);
+            dim3 bgrid((job->out_w + 8 * rtc::BLK_W - 1) / (8 * rtc::BLK_W),
+                       (job->out_h + 4 * rtc::BLK_H * rtc::SKYB_WARPS - 1) / (4 * rtc::BLK_H * rtc::SKYB_WARPS), planes);
+            CU(cudaFuncSetAttribute(rtc::render_skyblock_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)bsmem));
+            rtc::render_skyblock_kernel<<<bgrid, rtc::SKYB_THREADS, bsmem, st>>>(a, msc->tab, sw);
+            CU(cudaGetLastError());
+            return launch_paths(msc, a, msc->list, planes, 0, st);
+        }
         size_t smem = rtc::sky_smem_bytes(sc->ntris, sw.stream != 0);
         dim3 fgrid((job->out_w + rtc::FAST_LX * R - 1) / (rtc::FAST_LX * R),
                    (job->out_h + rtc::FAST_LY * rtc::FAST_WARPS - 1) / (rtc::FAST_LY * rtc::FAST_WARPS), planes);

@@ -31,9 +31,13 @@ struct PrimaryFrame {
     double Dmax;         // max |D| over the full image (a corner)
     double xstep;        // col_step / (H/2): dx distance between the R pixels of a lane
     int max_steps;       // R - 1
+    int block;           // 1: table for the block kernel (rtc_skyblock.cuh): {a, b, c_block, c_pixel}
+    double hw, hh;       // block mode: half extents of a lane's pixel block in (dx, dy), already inflated
 };
 
 // table: 4 x float4 per triangle, one per edge function: {a, b, c + margin, a * xstep}
+// (block mode: {a, b, c + margin + |a| hw + |b| hh, c + margin}: the .z constant bounds the edge function over a
+// whole pixel block from its value at the block centre, the .w constant is the per-pixel one)
 __global__ void prepare_primary_kernel(const DeviceScene sc, const PrimaryFrame fr, float4 *__restrict__ tab)
 {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -91,7 +95,15 @@ __global__ void prepare_primary_kernel(const DeviceScene sc, const PrimaryFrame 
         double eps = (8.0 + 2.0 * fr.max_steps) * range;
         double margin = 2.0 * u * (delta[k] * fr.Dmax + eps) + tiny * fr.Dmax + 1e-30;
         double cm = c + margin;
-        out[k] = make_float4((float)a, (float)b, (float)cm, (float)(a * fr.xstep));
+        if (fr.block) {
+            // E(x, y) <= E(centre) + |a| hw + |b| hh over the block; the float coefficients (float)a, (float)b
+            // are the ones the kernel multiplies with, their rounding is inside eps
+            double ext = (fabs(a) * fr.hw + fabs(b) * fr.hh) * 1.0000005 + 2.0 * u * range;
+            // the constants are rounded up so the float table entry is >= the real bound
+            out[k] = make_float4((float)a, (float)b, __double2float_ru(cm + ext), __double2float_ru(cm));
+        } else {
+            out[k] = make_float4((float)a, (float)b, (float)cm, (float)(a * fr.xstep));
+        }
         // too large / too small to reason about in float: let the exact path decide
         if (!isfinite(a) || !isfinite(b) || !isfinite(cm) || range > 1e30 || margin > 1e30)
             usable = false;
@@ -100,10 +112,10 @@ __global__ void prepare_primary_kernel(const DeviceScene sc, const PrimaryFrame 
         if (isfinite(tq) && tq == 0.0f) {
             // t = tq * inv = +-0 -> `dst < EPSILON` holds: a primary ray can never hit this triangle
             for (int k = 0; k < 4; ++k)
-                out[k] = make_float4(0.f, 0.f, -1.f, 0.f);
+                out[k] = make_float4(0.f, 0.f, -1.f, fr.block ? -1.f : 0.f);
         } else {
             for (int k = 0; k < 4; ++k)
-                out[k] = make_float4(0.f, 0.f, 1.f, 0.f); // always pass
+                out[k] = make_float4(0.f, 0.f, 1.f, fr.block ? 1.f : 0.f); // always pass
         }
     }
     for (int k = 0; k < 4; ++k)

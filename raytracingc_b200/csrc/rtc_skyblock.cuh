@@ -1,0 +1,304 @@
+// rtc_skyblock.cuh -- primary-ray kernel, block form (default when the scene has no spheres).
+//
+// Same job as render_sky_kernel (rtc_sky.cuh): classify pixels at the first sample, hand primary-hit pixels to
+// the path kernel, and run every sample's primary sweep for the pixels whose ray escapes.  The difference is the
+// granularity of the conservative test.  The four edge functions of a (camera, triangle) pair are affine in the
+// pixel's (dx, dy), so over a block of pixels
+//         max E_k  <=  E_k(block centre) + |a_k| * half_width + |b_k| * half_height ,
+// and the right-hand side (with the rounding margins of rtc_fast.cuh folded into its constant) is ONE pair of
+// FMAs.  A lane owns an 8 x 4 pixel block: if some E_k is negative at that bound, none of the block's 32 primary
+// rays can pass the reference's tests for this triangle (two-level conservative rasterisation: nothing is
+// approximated, every decision that reaches the image is taken by the reference's exact sequence).
+// Blocks that survive are expanded by the whole warp, one lane per pixel: per-pixel edge functions, then
+// tri_test_exact on the survivors, in triangle order (first index wins ties, raytracing.c:232).
+//
+// Warp = 8 x 4 lane-blocks = 64 x 16 pixels; CTA = 4 warps stacked in y = 64 x 64 pixels.
+#pragma once
+
+#include "rtc_sky.cuh"
+
+namespace rtc {
+
+constexpr int BLK_W = 8, BLK_H = 4;                 // pixels per lane-block
+constexpr int SKYB_WARPS = 4, SKYB_THREADS = 32 * SKYB_WARPS;
+constexpr int SKYB_CHUNK = 32;                      // triangles per candidate mask
+
+__host__ __device__ inline size_t skyblock_smem_bytes(int ntris, bool stream)
+{
+    return sky_smem_bytes(ntris, stream) + (size_t)SKYB_WARPS * 32 * 32 * sizeof(float2);
+}
+
+__global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const RenderArgs a,
+                                                                       const float4 *__restrict__ tab,
+                                                                       const SkyWork w)
+{
+    extern __shared__ float4 smem_dyn[];
+    __shared__ uint64_t bars[2];
+    const int ntris = a.sc.ntris;
+    const bool stream = w.stream != 0;
+    const int tile = stream ? w.tile : (ntris > 0 ? ntris : 1);
+    const int ntiles = (ntris + tile - 1) / tile;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float4 *sF = smem_dyn;
+    float2 *hitbuf = reinterpret_cast<float2 *>(sF + (stream ? 2 * SKY_TILE * 4 : 4 * (ntris > 0 ? ntris : 1))) +
+                     (size_t)warp * 32 * 32; // [lane-block][pixel] {best, id}
+
+    if (!stream) {
+        for (int i = threadIdx.x; i < 4 * ntris; i += SKYB_THREADS)
+            sF[i] = tab[i];
+    } else if (threadIdx.x == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        fence_barrier_init();
+    }
+    __syncthreads();
+
+    // this lane's block
+    const int ci0 = (blockIdx.x * 8 + (lane & 7)) * BLK_W;
+    const int cj0 = ((blockIdx.y * SKYB_WARPS + warp) * 4 + (lane >> 3)) * BLK_H;
+    const int g = a.split_first + blockIdx.z;
+    unsigned valid = 0;
+#pragma unroll
+    for (int p = 0; p < 32; ++p)
+        if (ci0 + (p & 7) < a.out_w && cj0 + (p >> 3) < a.out_h)
+            valid |= 1u << p;
+
+    const float fh = (float)(a.H / 2);
+    auto x_of = [&](int ci) { return a.col_start + ci * a.col_step; };
+    auto y_of = [&](int cj) { return a.row_start + (cj / a.band_h) * a.row_step + (cj % a.band_h); };
+    auto dx_at = [&](int ci) { return xdiv((float)(x_of(ci) - a.W / 2), fh); };
+    auto dy_at = [&](int cj) { return xdiv((float)(y_of(cj) - a.H / 2), fh); };
+    // block centre in (dx, dy): midpoint of the first and last pixel centres
+    const float cx = 0.5f * (dx_at(ci0) + dx_at(ci0 + BLK_W - 1));
+    const float cy = 0.5f * (dy_at(cj0) + dy_at(cj0 + BLK_H - 1));
+
+    const int s0 = (int)((long long)g * a.spp / a.nsplit), s1 = (int)((long long)(g + 1) * a.spp / a.nsplit);
+    const float wgt = (float)(1.0 / (double)a.spp);
+    unsigned sky = valid;  // pixels of this block still swept
+    unsigned mismatch = 0;
+    unsigned long long nrays = 0, nslow = 0, nhit = 0;
+    uint32_t k0 = 0;
+
+    auto issue = [&](uint32_t k, int t) {
+        const int n = min(tile, ntris - t * tile);
+        const uint32_t bytes = (uint32_t)n * 4u * (uint32_t)sizeof(float4);
+        fence_proxy_async();
+        mbar_arrive_expect_tx(&bars[k & 1], bytes);
+        tma_load_1d(sF + (size_t)(k & 1) * SKY_TILE * 4, tab + (size_t)t * tile * 4, bytes, &bars[k & 1]);
+    };
+
+    for (int s = s0; s < s1; ++s) {
+        bool touched = false; // this block's hitbuf entries are initialised for this sample
+        unsigned hits = 0;    // pixels of this block whose primary ray hit (this sample)
+        if (stream && threadIdx.x == 0) {
+            issue(k0, 0);
+            if (ntiles > 1)
+                issue(k0 + 1, 1);
+        }
+        const bool warp_busy = __any_sync(0xffffffffu, sky != 0);
+        for (int t = 0; t < ntiles; ++t) {
+            const float4 *F = sF;
+            int n = ntris, tbase = 0;
+            if (stream) {
+                const uint32_t k = k0 + (uint32_t)t;
+                mbar_wait(&bars[k & 1], (k >> 1) & 1u);
+                F = sF + (size_t)(k & 1) * SKY_TILE * 4;
+                n = min(tile, ntris - t * tile);
+                tbase = t * tile;
+            }
+            if (warp_busy) {
+                for (int c0 = 0; c0 < n; c0 += SKYB_CHUNK) {
+                    const int cn = min(SKYB_CHUNK, n - c0);
+                    // ---- block test of up to 32 triangles: branch-free, 8 FFMA + 4 integer ops each ----
+                    unsigned mask = 0;
+                    if (cn == SKYB_CHUNK) {
+#pragma unroll 8
+                        for (int j = 0; j < SKYB_CHUNK; ++j) {
+                            const float4 *f = F + 4 * (c0 + j);
+                            const float4 f0 = f[0], f1 = f[1], f2 = f[2], f3_ = f[3];
+                            const float e0 = fmaf(f0.x, cx, fmaf(f0.y, cy, f0.z));
+                            const float e1 = fmaf(f1.x, cx, fmaf(f1.y, cy, f1.z));
+                            const float e2 = fmaf(f2.x, cx, fmaf(f2.y, cy, f2.z));
+                            const float e3 = fmaf(f3_.x, cx, fmaf(f3_.y, cy, f3_.z));
+                            const int bits =
+                                __float_as_int(e0) | __float_as_int(e1) | __float_as_int(e2) | __float_as_int(e3);
+                            mask |= (bits >= 0) ? (1u << j) : 0u;
+                        }
+                    } else {
+                        for (int j = 0; j < cn; ++j) {
+                            const float4 *f = F + 4 * (c0 + j);
+                            const float4 f0 = f[0], f1 = f[1], f2 = f[2], f3_ = f[3];
+                            const float e0 = fmaf(f0.x, cx, fmaf(f0.y, cy, f0.z));
+                            const float e1 = fmaf(f1.x, cx, fmaf(f1.y, cy, f1.z));
+                            const float e2 = fmaf(f2.x, cx, fmaf(f2.y, cy, f2.z));
+                            const float e3 = fmaf(f3_.x, cx, fmaf(f3_.y, cy, f3_.z));
+                            const int bits =
+                                __float_as_int(e0) | __float_as_int(e1) | __float_as_int(e2) | __float_as_int(e3);
+                            mask |= (bits >= 0) ? (1u << j) : 0u;
+                        }
+                    }
+                    if (sky == 0)
+                        mask = 0;
+                    // ---- expand surviving blocks: the warp takes one block at a time, one lane per pixel ----
+                    unsigned pending = __ballot_sync(0xffffffffu, mask != 0);
+                    while (pending) {
+                        const int src = __ffs(pending) - 1;
+                        pending &= pending - 1;
+                        unsigned m = __shfl_sync(0xffffffffu, mask, src);
+                        const int bci0 = __shfl_sync(0xffffffffu, ci0, src);
+                        const int bcj0 = __shfl_sync(0xffffffffu, cj0, src);
+                        const unsigned bsky = __shfl_sync(0xffffffffu, sky, src);
+                        const bool btouched = __shfl_sync(0xffffffffu, (int)touched, src) != 0;
+                        const bool mine = (bsky >> lane) & 1u; // this lane's pixel of the block is swept
+                        const float dxr = dx_at(bci0 + (lane & 7)), dyr = dy_at(bcj0 + (lane >> 3));
+                        float2 *hb = hitbuf + src * 32 + lane;
+                        float best = 999999.0f;
+                        int id = -1;
+                        if (btouched) {
+                            const float2 h = *hb;
+                            best = h.x;
+                            id = __float_as_int(h.y);
+                        }
+                        f3 d = primary_dir(a, dxr, dyr);
+                        while (m) {
+                            const int j = __ffs(m) - 1;
+                            m &= m - 1;
+                            const int ti = tbase + c0 + j;
+                            const float4 *f = F + 4 * (c0 + j);
+                            const float4 f0 = f[0], f1 = f[1], f2 = f[2], f3_ = f[3];
+                            const float t0 = fmaf(f0.x, dxr, fmaf(f0.y, dyr, f0.w));
+                            const float t1 = fmaf(f1.x, dxr, fmaf(f1.y, dyr, f1.w));
+                            const float t2 = fmaf(f2.x, dxr, fmaf(f2.y, dyr, f2.w));
+                            const float t3 = fmaf(f3_.x, dxr, fmaf(f3_.y, dyr, f3_.w));
+                            const int bits =
+                                __float_as_int(t0) | __float_as_int(t1) | __float_as_int(t2) | __float_as_int(t3);
+                            if (bits >= 0 && mine) {
+                                unsigned dummy[1];
+                                tri_test_exact<false>(a.origin, d, __ldg(&a.sc.geo[3 * ti]), __ldg(&a.sc.geo[3 * ti + 1]),
+                                                      __ldg(&a.sc.geo[3 * ti + 2]), ti, best, id, dummy);
+                                nslow++;
+                            }
+                        }
+                        *hb = make_float2(best, __int_as_float(id));
+                        const unsigned hm = __ballot_sync(0xffffffffu, id != -1 && mine);
+                        if (lane == src) {
+                            touched = true;
+                            hits = hm; // best only improves: a later chunk's ballot includes earlier hits
+                            mask = 0;
+                        }
+                        __syncwarp();
+                    }
+                }
+            }
+            if (stream) {
+                __syncthreads();
+                if (threadIdx.x == 0 && t + 2 < ntiles)
+                    issue(k0 + (uint32_t)t + 2, t + 2);
+            }
+        }
+        k0 += (uint32_t)ntiles;
+        nrays += __popc(sky);
+
+        if (s == s0) {
+            // ---- classification: ids are final, hit pixels go to the path kernel's list ----
+            if (g == a.split_first) {
+                if (a.ids != nullptr) {
+                    for (int b = 0; b < 32; ++b) { // lane-block b of this warp, one lane per pixel
+                        const unsigned bvalid = __shfl_sync(0xffffffffu, valid, b);
+                        if (bvalid == 0)
+                            continue;
+                        const bool bt = __shfl_sync(0xffffffffu, (int)touched, b) != 0;
+                        const int bci0 = __shfl_sync(0xffffffffu, ci0, b), bcj0 = __shfl_sync(0xffffffffu, cj0, b);
+                        const int id = bt ? __float_as_int(hitbuf[b * 32 + lane].y) : -1;
+                        if ((bvalid >> lane) & 1u)
+                            a.ids[(size_t)(bcj0 + (lane >> 3)) * a.out_w + bci0 + (lane & 7)] = id;
+                    }
+                }
+                nhit = __popc(hits);
+                if (w.list != nullptr) {
+                    unsigned cnt = __popc(hits), incl = cnt;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        unsigned v = __shfl_up_sync(0xffffffffu, incl, o);
+                        if (lane >= o)
+                            incl += v;
+                    }
+                    const unsigned tot = __shfl_sync(0xffffffffu, incl, 31);
+                    if (tot) {
+                        unsigned base = 0;
+                        if (lane == 31)
+                            base = atomicAdd(w.list_count, tot);
+                        base = __shfl_sync(0xffffffffu, base, 31);
+                        unsigned off = base + incl - cnt, hm = hits;
+                        while (hm) {
+                            const int p = __ffs(hm) - 1;
+                            hm &= hm - 1;
+                            w.list[off++] = (cj0 + (p >> 3)) * a.out_w + ci0 + (p & 7);
+                        }
+                    }
+                }
+            }
+            sky &= ~hits;
+            nrays -= __popc(hits); // the classification sweep of a hit pixel is not a counted ray
+            const bool more = stream ? (__syncthreads_or(sky != 0) != 0) : __any_sync(0xffffffffu, sky != 0);
+            if (!more)
+                break;
+        } else {
+            mismatch |= hits;
+        }
+    }
+
+    // ---- sky pixels: spp identical contributions (same ray, no RNG draw), the reference's serial float adds;
+    //      one lane per pixel so the serial chains of 32 pixels run side by side ----
+    for (int b = 0; b < 32; ++b) {
+        const unsigned bsky = __shfl_sync(0xffffffffu, sky, b);
+        if (bsky == 0)
+            continue;
+        const int bci0 = __shfl_sync(0xffffffffu, ci0, b), bcj0 = __shfl_sync(0xffffffffu, cj0, b);
+        if (!((bsky >> lane) & 1u))
+            continue;
+        const int ci = bci0 + (lane & 7), cj = bcj0 + (lane >> 3);
+        f3 d = primary_dir(a, dx_at(ci), dy_at(cj));
+        f3 env = environment_light(d, a.sky);
+        f3 light = xadd3(mk3(0.f, 0.f, 0.f), xmul3(env, mk3(1.f, 1.f, 1.f))); // raytracing.c:291
+        f3 c = xscale3(light, wgt);
+        f3 acc = mk3(0.f, 0.f, 0.f);
+        for (int s = s0; s < s1; ++s)
+            acc = xadd3(acc, c);
+        const size_t pix = (size_t)cj * a.out_w + ci;
+        if (a.accum != nullptr) {
+            float *p = a.accum + ((size_t)blockIdx.z * a.out_w * a.out_h + pix) * 3;
+            p[0] = acc.x;
+            p[1] = acc.y;
+            p[2] = acc.z;
+        }
+        if (a.rgb != nullptr && a.nsplit == 1) {
+            uint8_t *p = a.rgb + pix * 3;
+            p[0] = (uint8_t)float_to_uint8(acc.x);
+            p[1] = (uint8_t)float_to_uint8(acc.y);
+            p[2] = (uint8_t)float_to_uint8(acc.z);
+        }
+    }
+
+    if (a.stats != nullptr) {
+        unsigned long long r_ = nrays, hp = nhit, sl = nslow, bad = __popc(mismatch);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            r_ += __shfl_xor_sync(0xffffffffu, r_, o);
+            hp += __shfl_xor_sync(0xffffffffu, hp, o);
+            sl += __shfl_xor_sync(0xffffffffu, sl, o);
+            bad += __shfl_xor_sync(0xffffffffu, bad, o);
+        }
+        if (lane == 0) {
+            atomicAdd(&a.stats[ST_RAYS], r_);
+            atomicAdd(&a.stats[ST_TRI_PAIRS], r_ * (unsigned long long)ntris);
+            atomicAdd(&a.stats[ST_SLOW_PAIRS], sl);
+            if (a.ids != nullptr)
+                atomicAdd(&a.stats[ST_HIT_PIXELS], hp);
+            if (bad)
+                atomicAdd(&a.stats[ST_MISMATCH], bad);
+        }
+    }
+}
+
+} // namespace rtc

@@ -49,11 +49,12 @@ def test_fast_equals_exact_random(case):
     cam = rtc.camera_look_at(origin, look_at, fov)
     for tonly in (1, 0):
         kw = dict(width=W, height=H, spp=spp, max_bounce=bounce, triangles_only=tonly, camera=cam, want_ids=True)
-        rgb_f, ids_f, st_f = rtc.render(tris, **kw)
         rgb_e, ids_e, st_e = rtc.render(tris, flags=api.RTC_FLAG_EXACT_ONLY, **kw)
-        assert (ids_f == ids_e).all(), f"case {case}: {(ids_f != ids_e).sum()} ids differ"
-        assert st_f["rays"] == st_e["rays"]
-        assert (rgb_f == rgb_e).all(), f"case {case}: {(rgb_f != rgb_e).any(axis=-1).sum()} pixels differ"
+        for fl in (0, api.RTC_FLAG_PER_PAIR_FILTER, api.RTC_FLAG_PATHS_ONLY):  # block filter, per-pair filter, none
+            rgb_f, ids_f, st_f = rtc.render(tris, flags=fl, **kw)
+            assert (ids_f == ids_e).all(), f"case {case} flags {fl}: {(ids_f != ids_e).sum()} ids differ"
+            assert st_f["rays"] == st_e["rays"]
+            assert (rgb_f == rgb_e).all(), f"case {case} flags {fl}: {(rgb_f != rgb_e).any(axis=-1).sum()} pixels differ"
 
 
 def test_pixel_centre_edges():
@@ -90,7 +91,8 @@ def test_pixel_centre_edges():
             nrm = -nrm
         tris[i] = (A, B, C, nrm.astype(np.float32), (0.8, 0.7, 0.6), 0.0, 0.3)
     kw = dict(width=W, height=H, spp=3, max_bounce=3, camera=cam, want_ids=True)
-    rgb_f, ids_f, st_f = rtc.render(tris, **kw)
     rgb_e, ids_e, st_e = rtc.render(tris, flags=api.RTC_FLAG_EXACT_ONLY, **kw)
-    assert (ids_f == ids_e).all() and (rgb_f == rgb_e).all() and st_f["rays"] == st_e["rays"]
-    assert (ids_f >= 0).sum() > 100
+    for fl in (0, api.RTC_FLAG_PER_PAIR_FILTER):
+        rgb_f, ids_f, st_f = rtc.render(tris, flags=fl, **kw)
+        assert (ids_f == ids_e).all() and (rgb_f == rgb_e).all() and st_f["rays"] == st_e["rays"]
+    assert (ids_e >= 0).sum() > 100
