@@ -83,6 +83,7 @@ struct RtcScene {
     int nsm = 0;
     int *list = nullptr;          // per-frame work list of primary-hit pixels (sky kernel -> path kernel)
     size_t cap_list = 0;
+    float2 *rec = nullptr;        // primary-hit record of each listed pixel
     unsigned *counters = nullptr; // [0] list length, [1] path-kernel work cursor
 };
 
@@ -153,6 +154,7 @@ void rtc_scene_destroy(RtcScene *sc)
     cudaFree(sc->raw);
     cudaFree(sc->tab);
     cudaFree(sc->list);
+    cudaFree(sc->rec);
     cudaFree(sc->counters);
     delete sc;
 }
@@ -359,9 +361,12 @@ int ensure_scratch(RtcScene *sc, size_t npix)
     if (!sc->counters)
         CU(cudaMalloc(&sc->counters, 4 * sizeof(unsigned)));
     if (npix > sc->cap_list || !sc->list) {
-        cudaFree(sc->list);
+        CU(cudaFree(sc->list));
         sc->list = nullptr;
         CU(cudaMalloc(&sc->list, sizeof(int) * (npix ? npix : 1)));
+        CU(cudaFree(sc->rec));
+        sc->rec = nullptr;
+        CU(cudaMalloc(&sc->rec, sizeof(float2) * (npix ? npix : 1)));
         sc->cap_list = npix;
     }
     if (!sc->nsm) {
@@ -372,10 +377,12 @@ int ensure_scratch(RtcScene *sc, size_t npix)
 }
 
 // the path kernel: persistent grid over a work list (list == nullptr: every pixel of the subset)
-int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, int planes, int write_ids, cudaStream_t st)
+int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const float2 *rec, int planes, int write_ids,
+                 cudaStream_t st)
 {
     rtc::PathWork w;
     w.list = list;
+    w.rec = rec;
     w.list_count = sc->counters;
     w.cursor = sc->counters + 1;
     w.planes = planes;
@@ -486,6 +493,12 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
     if (G > 1 && !d_accum)
         return fail(RTC_ERR_ARG, "render: nsplit > 1 needs d_accum (planes of partial sums)");
     CU(cudaSetDevice(sc->device));
+    {
+        // a stale error of an earlier, unrelated runtime call must not be blamed on the launches below
+        cudaError_t stale = cudaGetLastError();
+        if (stale != cudaSuccess && getenv("RTC_TRACE"))
+            fprintf(stderr, "rtc_b200: cleared stale CUDA error before render: %s\n", cudaGetErrorString(stale));
+    }
     rtc::RenderArgs a = make_args(sc, sky, cam, job);
     a.rgb = d_rgb;
     a.accum = d_accum;
@@ -501,7 +514,7 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
     }
     if (R > 0) {
         if (sc->ntris > msc->cap_tab || !msc->tab) {
-            cudaFree(msc->tab);
+            CU(cudaFree(msc->tab));
             msc->tab = nullptr;
             CU(cudaMalloc(&msc->tab, sizeof(float4) * 4 * (size_t)(sc->ntris > 0 ? sc->ntris : 1)));
             msc->cap_tab = sc->ntris > 0 ? sc->ntris : 1;
@@ -518,6 +531,7 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
         rtc::SkyWork sw;
         sw.list = msc->list;
         sw.list_count = msc->counters;
+        sw.rec = msc->rec;
         sw.tile = env_int("RTC_SKY_TILE", rtc::SKY_TILE);
         if (sw.tile < 1 || sw.tile > rtc::SKY_TILE)
             sw.tile = rtc::SKY_TILE;
@@ -530,7 +544,7 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
                                     (int)bsmem));
             rtc::render_skyblock_kernel<<<bgrid, rtc::SKYB_THREADS, bsmem, st>>>(a, msc->tab, sw);
             CU(cudaGetLastError());
-            return launch_paths(msc, a, msc->list, planes, 0, st);
+            return launch_paths(msc, a, msc->list, msc->rec, planes, 0, st);
         }
         size_t smem = rtc::sky_smem_bytes(sc->ntris, sw.stream != 0);
         dim3 fgrid((job->out_w + rtc::FAST_LX * R - 1) / (rtc::FAST_LX * R),
@@ -553,12 +567,12 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
             LAUNCH_SKY(1);
 #undef LAUNCH_SKY
         CU(cudaGetLastError());
-        return launch_paths(msc, a, msc->list, planes, 0, st);
+        return launch_paths(msc, a, msc->list, nullptr, planes, 0, st);
     }
     if (job->flags & RTC_FLAG_PATHS_ONLY) {
         if (job->maxBounce < 1)
             return fail(RTC_ERR_ARG, "RTC_FLAG_PATHS_ONLY needs maxBounce >= 1");
-        return launch_paths(msc, a, nullptr, planes, 1, st);
+        return launch_paths(msc, a, nullptr, nullptr, planes, 1, st);
     }
     dim3 grid((job->out_w + rtc::CTA_W - 1) / rtc::CTA_W, (job->out_h + rtc::CTA_H - 1) / rtc::CTA_H, planes);
     if (job->flags & RTC_FLAG_COUNT_EXITS)

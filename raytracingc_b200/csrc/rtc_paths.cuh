@@ -30,6 +30,9 @@ struct PathWork {
     int planes;                 // sub-streams rendered by this launch
     int write_ids;              // 1: this kernel owns the primary-id map (no sky kernel ran)
     int tile;                   // triangles per streamed tile (<= PATH_TILE), STREAM only
+    const float2 *rec;          // with a list: {distance, id bits} of each listed pixel's primary hit, found by the
+                                // primary kernel, which also re-sweeps that ray every sample; nullptr: the path
+                                // kernel sweeps primary rays itself
 };
 
 __host__ __device__ inline size_t path_smem_bytes(int ntris, bool stream)
@@ -37,14 +40,19 @@ __host__ __device__ inline size_t path_smem_bytes(int ntris, bool stream)
     return stream ? (size_t)2 * PATH_TILE * 3 * sizeof(float4) : (size_t)(ntris > 0 ? ntris : 1) * 3 * sizeof(float4);
 }
 
-// The reference's ray-triangle test arranged for SIMT (same operations, same order, same decisions): the values
-// up to s.h are computed straight-line for every pair -- independent work across unrolled triangles -- and the
-// exits are taken on those exact values.  Two exits are decided without the division:
-//   * sign(s.h) != sign(det), |s.h| >= 1e-30, |det| <= 2^20  =>  u = fl(s.h * fl(1/det)) < 0   (cannot round to -0)
-//   * same sign and |s.h| > |det| * 1.00001                     =>  u > 1                       (margin >> 3 roundings)
-// Every other pair continues with the reference's remaining operations.
-__device__ __forceinline__ void tri_test_sl(const f3 &o, const f3 &d, const float4 &p0, const float4 &p1,
-                                            const float4 &p2, int idx, float &best, int &bestId)
+// The reference's ray-triangle test arranged for SIMT, in two phases per chunk of 32 triangles.
+//
+// Phase 1 (tri_quick, branch-free, warp-uniform shared-memory reads): the reference's own values c = d.n,
+// h = d x AC, det = AB.h, s = o - A, s.h -- same operations, same order -- are computed for every pair and
+// the pair is dropped when the reference provably drops it:
+//   * c >= 0                                  (cull, raytracing.c:189)
+//   * |det| < EPS                             (raytracing.c:195; -EPS < det < EPS  <=>  |det| < EPS)
+//   * t = s.h with det's sign;  t < -1e-30 and |det| <= 2^20   =>  u = fl(s.h * fl(1/det)) < 0  (cannot round to -0)
+//   *                           t > |det| * 1.00001              =>  u > 1   (margin >> the 3 roundings of u)
+// NaNs never drop a pair (every comparison is written so that an unordered result keeps it).
+// Phase 2: each lane walks the set bits of its survivor mask in index order and runs the reference's full
+// sequence (tri_test_exact) on them, so distances, ties (first index wins) and ids are the reference's.
+__device__ __forceinline__ bool tri_quick(const f3 &o, const f3 &d, const float4 &p0, const float4 &p1, const float4 &p2)
 {
     const f3 n = mk3(p0.w, p1.w, p2.w);
     const f3 AB = mk3(p1.x, p1.y, p1.z), AC = mk3(p2.x, p2.y, p2.z);
@@ -53,25 +61,40 @@ __device__ __forceinline__ void tri_test_sl(const f3 &o, const f3 &d, const floa
     const float det = xdot(AB, h);
     const f3 s = xsub3(o, mk3(p0.x, p0.y, p0.z));
     const float sh = xdot(s, h);
-    const bool cont = !(c >= 0.0f) && !(fabsf(det) < 0.001f); // -EPS < det < EPS  <=>  |det| < EPS
-    const float adet = fabsf(det), ash = fabsf(sh);
-    const bool opp = (__float_as_int(sh) ^ __float_as_int(det)) < 0;
-    const bool rej = opp ? (ash >= 1e-30f && adet <= 1048576.0f) : (ash > xmul(adet, 1.00001f));
-    if (cont && !rej) {
-        const float inv = xrcp(det);
-        const float u = xmul(sh, inv);
-        if (u < 0.0f || u > 1.0f)
-            return;
-        const f3 q = xcross(s, AB);
-        const float v = xmul(xdot(d, q), inv);
-        if (v < 0.0f || xadd(u, v) > 1.0f)
-            return;
-        const float dst = xmul(xdot(AC, q), inv);
-        if (dst < 0.001f)
-            return;
-        if (dst < best) { // strict <: first index wins ties (raytracing.c:232)
-            best = dst;
-            bestId = idx;
+    const float adet = fabsf(det);
+    const float t = __int_as_float(__float_as_int(sh) ^ (__float_as_int(det) & 0x80000000)); // s.h * sign(det)
+    const float m = adet * 1.00001f;
+    bool keep = !(adet <= 1048576.0f);    // huge |det| (or NaN): never drop on the negative side
+    keep = keep || !(t < -1e-30f);
+    keep = keep && !(t > m);
+    keep = keep && !(adet < 0.001f);
+    keep = keep && !(c >= 0.0f);
+    return keep;
+}
+
+template <typename GeoPtr>
+__device__ __forceinline__ void sweep_chunked(const GeoPtr S, int n, int base, bool active, const f3 &o, const f3 &d,
+                                              float &best, int &bestId)
+{
+    for (int c0 = 0; c0 < n; c0 += 32) {
+        const int cn = min(32, n - c0);
+        unsigned m = 0;
+        if (active) {
+            if (cn == 32) {
+#pragma unroll 8
+                for (int j = 0; j < 32; ++j)
+                    m |= tri_quick(o, d, S[3 * (c0 + j)], S[3 * (c0 + j) + 1], S[3 * (c0 + j) + 2]) ? (1u << j) : 0u;
+            } else {
+                for (int j = 0; j < cn; ++j)
+                    m |= tri_quick(o, d, S[3 * (c0 + j)], S[3 * (c0 + j) + 1], S[3 * (c0 + j) + 2]) ? (1u << j) : 0u;
+            }
+        }
+        while (m) {
+            const int j = __ffs(m) - 1;
+            m &= m - 1;
+            unsigned dummy[1];
+            tri_test_exact<false>(o, d, S[3 * (c0 + j)], S[3 * (c0 + j) + 1], S[3 * (c0 + j) + 2], base + c0 + j, best,
+                                  bestId, dummy);
         }
     }
 }
@@ -105,7 +128,10 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
     Lane L;
     f3 pdir = mk3(0.f, 0.f, 0.f);
     int pix = 0, plane = 0, s_end = 0;
-    bool active = false, exhausted = false, first = false;
+    bool active = false, exhausted = false, first = false, fresh = false;
+    const bool has_rec = w.rec != nullptr;
+    float best0 = 999999.0f;
+    int id0 = -1;
     unsigned long long nrays = 0, nhitpix = 0;
     uint32_t k0 = 0; // tiles consumed so far (STREAM): stage = k & 1, parity = (k >> 1) & 1
 
@@ -115,6 +141,34 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
         fence_proxy_async();
         mbar_arrive_expect_tx(&bars[k & 1], bytes);
         tma_load_1d(sGeo + (size_t)(k & 1) * PATH_TILE * 3, a.sc.geo + (size_t)t * tile * 3, bytes, &bars[k & 1]);
+    };
+
+    // a path has ended: accumulate it (main.c:99) and start the next sample, or finish the pixel
+    auto finish_sample = [&]() {
+        L.acc = xadd3(L.acc, xscale3(L.light, wgt));
+        L.sample++;
+        if (L.sample >= s_end) {
+            active = false;
+            if (a.accum != nullptr) {
+                float *p = a.accum + ((size_t)plane * a.out_w * a.out_h + pix) * 3;
+                p[0] = L.acc.x;
+                p[1] = L.acc.y;
+                p[2] = L.acc.z;
+            }
+            if (a.rgb != nullptr && a.nsplit == 1) { // vec3ToColor, raytracing.c:11-15
+                uint8_t *p = a.rgb + (size_t)pix * 3;
+                p[0] = (uint8_t)float_to_uint8(L.acc.x);
+                p[1] = (uint8_t)float_to_uint8(L.acc.y);
+                p[2] = (uint8_t)float_to_uint8(L.acc.z);
+            }
+        } else {
+            L.pos = a.origin;
+            L.dir = pdir;
+            L.tint = mk3(1.f, 1.f, 1.f);
+            L.light = mk3(0.f, 0.f, 0.f);
+            L.bounce = 0;
+            fresh = true;
+        }
     };
 
     while (true) {
@@ -149,6 +203,12 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
                         s_end = (int)((long long)(g + 1) * a.spp / a.nsplit);
                         L.bounce = 0;
                         first = true;
+                        fresh = true;
+                        if (has_rec) {
+                            const float2 r = w.rec[t % npix];
+                            best0 = r.x;
+                            id0 = __float_as_int(r.y);
+                        }
                         active = L.sample < s_end;
                         if (!active) { // empty sample range: the pixel's partial sum is zero
                             if (a.accum != nullptr) {
@@ -162,6 +222,14 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
                 }
             }
         }
+        // ---- known primary hit: shade it without a sweep (the primary kernel sweeps that ray every sample) ----
+        if (has_rec) {
+            while (active && fresh) {
+                fresh = false;
+                if (shade(L, a, best0, id0))
+                    finish_sample();
+            }
+        }
         const bool any = STREAM ? (__syncthreads_or(active) != 0) : __any_sync(0xffffffffu, active);
         if (!any)
             break;
@@ -173,11 +241,7 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
             for (int k = 0; k < nsph; ++k)
                 sphere_test_exact(L.pos, L.dir, __ldg(&a.sc.s0[k]), k, best, bestId);
         if (!STREAM) {
-            if (active) {
-#pragma unroll 4
-                for (int i = 0; i < ntris; ++i)
-                    tri_test_sl(L.pos, L.dir, sGeo[3 * i], sGeo[3 * i + 1], sGeo[3 * i + 2], i, best, bestId);
-            }
+            sweep_chunked(sGeo, ntris, 0, active, L.pos, L.dir, best, bestId);
         } else {
             if (threadIdx.x == 0) {
                 issue(k0, 0);
@@ -187,13 +251,8 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
             for (int t = 0; t < ntiles; ++t) {
                 const uint32_t k = k0 + (uint32_t)t;
                 mbar_wait(&bars[k & 1], (k >> 1) & 1u);
-                if (active) {
-                    const float4 *S = sGeo + (size_t)(k & 1) * PATH_TILE * 3;
-                    const int n = min(tile, ntris - t * tile), base = t * tile;
-#pragma unroll 4
-                    for (int i = 0; i < n; ++i)
-                        tri_test_sl(L.pos, L.dir, S[3 * i], S[3 * i + 1], S[3 * i + 2], base + i, best, bestId);
-                }
+                sweep_chunked(sGeo + (size_t)(k & 1) * PATH_TILE * 3, min(tile, ntris - t * tile), t * tile,
+                              active, L.pos, L.dir, best, bestId);
                 __syncthreads(); // every warp is done with this stage
                 if (threadIdx.x == 0 && t + 2 < ntiles)
                     issue(k + 2, t + 2);
@@ -212,31 +271,9 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
                     nhitpix += bestId != -1;
                 }
             }
-            if (shade(L, a, best, bestId)) {
-                L.acc = xadd3(L.acc, xscale3(L.light, wgt)); // main.c:99
-                L.sample++;
-                if (L.sample >= s_end) {
-                    active = false;
-                    if (a.accum != nullptr) {
-                        float *p = a.accum + ((size_t)plane * a.out_w * a.out_h + pix) * 3;
-                        p[0] = L.acc.x;
-                        p[1] = L.acc.y;
-                        p[2] = L.acc.z;
-                    }
-                    if (a.rgb != nullptr && a.nsplit == 1) { // vec3ToColor, raytracing.c:11-15
-                        uint8_t *p = a.rgb + (size_t)pix * 3;
-                        p[0] = (uint8_t)float_to_uint8(L.acc.x);
-                        p[1] = (uint8_t)float_to_uint8(L.acc.y);
-                        p[2] = (uint8_t)float_to_uint8(L.acc.z);
-                    }
-                } else {
-                    L.pos = a.origin;
-                    L.dir = pdir;
-                    L.tint = mk3(1.f, 1.f, 1.f);
-                    L.light = mk3(0.f, 0.f, 0.f);
-                    L.bounce = 0;
-                }
-            }
+            fresh = false;
+            if (shade(L, a, best, bestId))
+                finish_sample();
         }
     }
 

@@ -27,6 +27,7 @@ constexpr int SKY_TILE = 512; // triangles per table tile: 32 KB per stage
 struct SkyWork {
     int *list;            // out: compact indices of primary-hit pixels (nullptr: do not build a list)
     unsigned *list_count; // out: number of entries (zeroed before the launch)
+    float2 *rec;          // out (block kernel): {distance, id bits} of each listed pixel's primary hit
     int tile;             // triangles per streamed tile (<= SKY_TILE)
     int stream;           // 1: stream the table per sample; 0: resident (needs ntris <= SKY_TILE)
 };

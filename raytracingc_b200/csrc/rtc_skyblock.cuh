@@ -1,8 +1,10 @@
 // rtc_skyblock.cuh -- primary-ray kernel, block form (default when the scene has no spheres).
 //
-// Same job as render_sky_kernel (rtc_sky.cuh): classify pixels at the first sample, hand primary-hit pixels to
-// the path kernel, and run every sample's primary sweep for the pixels whose ray escapes.  The difference is the
-// granularity of the conservative test.  The four edge functions of a (camera, triangle) pair are affine in the
+// Owns EVERY primary ray of the frame: the first sample classifies the pixels (primary-hit pixels go to the path
+// kernel's work list together with their hit record {distance, id}; sky pixels are finished here), and every
+// sample re-sweeps every pixel's primary ray, as the reference does (main.c:98-99), cross-checking the result
+// against the classification.  The path kernel (rtc_paths.cuh) then only sweeps bounce rays.  Compared with
+// render_sky_kernel (rtc_sky.cuh) the difference is the granularity of the conservative test.  The four edge functions of a (camera, triangle) pair are affine in the
 // pixel's (dx, dy), so over a block of pixels
 //         max E_k  <=  E_k(block centre) + |a_k| * half_width + |b_k| * half_height ,
 // and the right-hand side (with the rounding margins of rtc_fast.cuh folded into its constant) is ONE pair of
@@ -74,7 +76,7 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
 
     const int s0 = (int)((long long)g * a.spp / a.nsplit), s1 = (int)((long long)(g + 1) * a.spp / a.nsplit);
     const float wgt = (float)(1.0 / (double)a.spp);
-    unsigned sky = valid;  // pixels of this block still swept
+    unsigned hits0 = 0;    // classification: pixels of this block whose primary ray hits
     unsigned mismatch = 0;
     unsigned long long nrays = 0, nslow = 0, nhit = 0;
     uint32_t k0 = 0;
@@ -95,7 +97,7 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
             if (ntiles > 1)
                 issue(k0 + 1, 1);
         }
-        const bool warp_busy = __any_sync(0xffffffffu, sky != 0);
+        const bool warp_busy = __any_sync(0xffffffffu, valid != 0);
         for (int t = 0; t < ntiles; ++t) {
             const float4 *F = sF;
             int n = ntris, tbase = 0;
@@ -137,7 +139,7 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
                             mask |= (bits >= 0) ? (1u << j) : 0u;
                         }
                     }
-                    if (sky == 0)
+                    if (valid == 0)
                         mask = 0;
                     // ---- expand surviving blocks: the warp takes one block at a time, one lane per pixel ----
                     unsigned pending = __ballot_sync(0xffffffffu, mask != 0);
@@ -147,7 +149,7 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
                         unsigned m = __shfl_sync(0xffffffffu, mask, src);
                         const int bci0 = __shfl_sync(0xffffffffu, ci0, src);
                         const int bcj0 = __shfl_sync(0xffffffffu, cj0, src);
-                        const unsigned bsky = __shfl_sync(0xffffffffu, sky, src);
+                        const unsigned bsky = __shfl_sync(0xffffffffu, valid, src);
                         const bool btouched = __shfl_sync(0xffffffffu, (int)touched, src) != 0;
                         const bool mine = (bsky >> lane) & 1u; // this lane's pixel of the block is swept
                         const float dxr = dx_at(bci0 + (lane & 7)), dyr = dy_at(bcj0 + (lane >> 3));
@@ -197,7 +199,7 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
             }
         }
         k0 += (uint32_t)ntiles;
-        nrays += __popc(sky);
+        nrays += __popc(valid);
 
         if (s == s0) {
             // ---- classification: ids are final, hit pixels go to the path kernel's list ----
@@ -233,23 +235,22 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
                         while (hm) {
                             const int p = __ffs(hm) - 1;
                             hm &= hm - 1;
-                            w.list[off++] = (cj0 + (p >> 3)) * a.out_w + ci0 + (p & 7);
+                            w.list[off] = (cj0 + (p >> 3)) * a.out_w + ci0 + (p & 7);
+                            w.rec[off] = hitbuf[lane * 32 + p]; // {distance, id} of the primary hit
+                            ++off;
                         }
                     }
                 }
             }
-            sky &= ~hits;
-            nrays -= __popc(hits); // the classification sweep of a hit pixel is not a counted ray
-            const bool more = stream ? (__syncthreads_or(sky != 0) != 0) : __any_sync(0xffffffffu, sky != 0);
-            if (!more)
-                break;
+            hits0 = hits;
         } else {
-            mismatch |= hits;
+            mismatch |= hits ^ hits0; // same ray, same arithmetic: every sample must reproduce the classification
         }
     }
 
     // ---- sky pixels: spp identical contributions (same ray, no RNG draw), the reference's serial float adds;
     //      one lane per pixel so the serial chains of 32 pixels run side by side ----
+    const unsigned sky = valid & ~hits0;
     for (int b = 0; b < 32; ++b) {
         const unsigned bsky = __shfl_sync(0xffffffffu, sky, b);
         if (bsky == 0)
