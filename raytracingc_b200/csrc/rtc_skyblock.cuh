@@ -4,13 +4,15 @@
 // kernel's work list together with their hit record {distance, id}; sky pixels are finished here), and every
 // sample re-sweeps every pixel's primary ray, as the reference does (main.c:98-99), cross-checking the result
 // against the classification.  The path kernel (rtc_paths.cuh) then only sweeps bounce rays.  Compared with
-// render_sky_kernel (rtc_sky.cuh) the difference is the granularity of the conservative test.  The four edge functions of a (camera, triangle) pair are affine in the
-// pixel's (dx, dy), so over a block of pixels
+// render_sky_kernel (rtc_sky.cuh) the difference is the granularity of the conservative test.
+// The four edge functions of a (camera, triangle) pair are affine in the pixel's (dx, dy), so over a block of pixels
 //         max E_k  <=  E_k(block centre) + |a_k| * half_width + |b_k| * half_height ,
 // and the right-hand side (with the rounding margins of rtc_fast.cuh folded into its constant) is ONE pair of
 // FMAs.  A lane owns an 8 x 4 pixel block: if some E_k is negative at that bound, none of the block's 32 primary
 // rays can pass the reference's tests for this triangle (two-level conservative rasterisation: nothing is
 // approximated, every decision that reaches the image is taken by the reference's exact sequence).
+// One level above, lane j first bounds triangle j of each 32-triangle chunk over the warp's whole 64 x 16 region
+// (same inequality, the spread of the block centres added), so only triangles near the warp are block-tested.
 // Blocks that survive are expanded by the whole warp, one lane per pixel: per-pixel edge functions, then
 // tri_test_exact on the survivors, in triangle order (first index wins ties, raytracing.c:232).
 //
@@ -73,6 +75,12 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
     // block centre in (dx, dy): midpoint of the first and last pixel centres
     const float cx = 0.5f * (dx_at(ci0) + dx_at(ci0 + BLK_W - 1));
     const float cy = 0.5f * (dy_at(cj0) + dy_at(cj0 + BLK_H - 1));
+    // the warp's region: block centres span [wcx - ehw, wcx + ehw] x [wcy - ehh, wcy + ehh] (inflated for rounding)
+    const float cx_lo = __shfl_sync(0xffffffffu, cx, 0), cx_hi = __shfl_sync(0xffffffffu, cx, 7);
+    const float cy_lo = __shfl_sync(0xffffffffu, cy, 0), cy_hi = __shfl_sync(0xffffffffu, cy, 24);
+    const float wcx = 0.5f * (cx_lo + cx_hi), wcy = 0.5f * (cy_lo + cy_hi);
+    const float ehw = 0.5f * (cx_hi - cx_lo) * 1.001f + 1e-6f * (1.0f + fabsf(wcx));
+    const float ehh = 0.5f * (cy_hi - cy_lo) * 1.001f + 1e-6f * (1.0f + fabsf(wcy));
 
     const int s0 = (int)((long long)g * a.spp / a.nsplit), s1 = (int)((long long)(g + 1) * a.spp / a.nsplit);
     const float wgt = (float)(1.0 / (double)a.spp);
@@ -111,33 +119,32 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
             if (warp_busy) {
                 for (int c0 = 0; c0 < n; c0 += SKYB_CHUNK) {
                     const int cn = min(SKYB_CHUNK, n - c0);
-                    // ---- block test of up to 32 triangles: branch-free, 8 FFMA + 4 integer ops each ----
+                    // ---- level 1: lane j bounds triangle c0 + j over the WARP's whole 64 x 16 pixel region ----
+                    bool wpass = false;
+                    if (lane < cn) {
+                        const float4 *f = F + 4 * (c0 + lane);
+                        const float4 f0 = f[0], f1 = f[1], f2 = f[2], f3_ = f[3];
+                        const float e0 = fmaf(fabsf(f0.x), ehw, fmaf(fabsf(f0.y), ehh, fmaf(f0.x, wcx, fmaf(f0.y, wcy, f0.z))));
+                        const float e1 = fmaf(fabsf(f1.x), ehw, fmaf(fabsf(f1.y), ehh, fmaf(f1.x, wcx, fmaf(f1.y, wcy, f1.z))));
+                        const float e2 = fmaf(fabsf(f2.x), ehw, fmaf(fabsf(f2.y), ehh, fmaf(f2.x, wcx, fmaf(f2.y, wcy, f2.z))));
+                        const float e3 =
+                            fmaf(fabsf(f3_.x), ehw, fmaf(fabsf(f3_.y), ehh, fmaf(f3_.x, wcx, fmaf(f3_.y, wcy, f3_.z))));
+                        wpass = (__float_as_int(e0) | __float_as_int(e1) | __float_as_int(e2) | __float_as_int(e3)) >= 0;
+                    }
+                    unsigned wm = __ballot_sync(0xffffffffu, wpass);
+                    // ---- level 2: every lane bounds the surviving triangles over its own 8 x 4 pixel block ----
                     unsigned mask = 0;
-                    if (cn == SKYB_CHUNK) {
-#pragma unroll 8
-                        for (int j = 0; j < SKYB_CHUNK; ++j) {
-                            const float4 *f = F + 4 * (c0 + j);
-                            const float4 f0 = f[0], f1 = f[1], f2 = f[2], f3_ = f[3];
-                            const float e0 = fmaf(f0.x, cx, fmaf(f0.y, cy, f0.z));
-                            const float e1 = fmaf(f1.x, cx, fmaf(f1.y, cy, f1.z));
-                            const float e2 = fmaf(f2.x, cx, fmaf(f2.y, cy, f2.z));
-                            const float e3 = fmaf(f3_.x, cx, fmaf(f3_.y, cy, f3_.z));
-                            const int bits =
-                                __float_as_int(e0) | __float_as_int(e1) | __float_as_int(e2) | __float_as_int(e3);
-                            mask |= (bits >= 0) ? (1u << j) : 0u;
-                        }
-                    } else {
-                        for (int j = 0; j < cn; ++j) {
-                            const float4 *f = F + 4 * (c0 + j);
-                            const float4 f0 = f[0], f1 = f[1], f2 = f[2], f3_ = f[3];
-                            const float e0 = fmaf(f0.x, cx, fmaf(f0.y, cy, f0.z));
-                            const float e1 = fmaf(f1.x, cx, fmaf(f1.y, cy, f1.z));
-                            const float e2 = fmaf(f2.x, cx, fmaf(f2.y, cy, f2.z));
-                            const float e3 = fmaf(f3_.x, cx, fmaf(f3_.y, cy, f3_.z));
-                            const int bits =
-                                __float_as_int(e0) | __float_as_int(e1) | __float_as_int(e2) | __float_as_int(e3);
-                            mask |= (bits >= 0) ? (1u << j) : 0u;
-                        }
+                    while (wm) {
+                        const int j = __ffs(wm) - 1;
+                        wm &= wm - 1;
+                        const float4 *f = F + 4 * (c0 + j);
+                        const float4 f0 = f[0], f1 = f[1], f2 = f[2], f3_ = f[3];
+                        const float e0 = fmaf(f0.x, cx, fmaf(f0.y, cy, f0.z));
+                        const float e1 = fmaf(f1.x, cx, fmaf(f1.y, cy, f1.z));
+                        const float e2 = fmaf(f2.x, cx, fmaf(f2.y, cy, f2.z));
+                        const float e3 = fmaf(f3_.x, cx, fmaf(f3_.y, cy, f3_.z));
+                        const int bits = __float_as_int(e0) | __float_as_int(e1) | __float_as_int(e2) | __float_as_int(e3);
+                        mask |= (bits >= 0) ? (1u << j) : 0u;
                     }
                     if (valid == 0)
                         mask = 0;
