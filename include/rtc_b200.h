@@ -44,6 +44,7 @@ extern "C" {
                                    operation sequence (validation mode)          */
 #define RTC_FLAG_PER_PAIR_FILTER 8u /* primary pre-filter evaluated per (pixel, triangle) pair instead of
                                       per (8x4 pixel block, triangle) + expansion of surviving blocks */
+#define RTC_FLAG_TIME_KERNELS 16u /* record CUDA events around the primary and the path kernel (rtc_scene_kernel_times) */
 #define RTC_FLAG_PATHS_ONLY 4u  /* no primary pre-filter: every pixel goes through the
                                    path kernel (exact arithmetic, shared-memory tiles) */
 
@@ -105,6 +106,10 @@ void render_cuda_shutdown(void);
 void rtc_camera_look_at(const float origin[3], const float lookingAt[3], float fov, Camera *out);
 /* normalized() of reference moremath.c:12-18, e.g. for the sun (main.c:247) */
 void rtc_normalize(const float in[3], float out[3]);
+
+/* Host code: the synthetic random-triangle scene of BASELINE.json's config 5 (splitmix64, definition in
+ * rtc_api.cu / DESIGN.md; the reference has no generator).  The config uses seed 0xB200, ntris 1048576. */
+void rtc_synth_scene(uint64_t seed, int32_t ntris, Triangle *out);
 
 /* number of CUDA devices visible (0 if none / no driver) */
 int rtc_device_count(void);
@@ -183,6 +188,11 @@ int rtc_sum_quantize_device(int device, const float *d_planes, int nplanes, size
 
 /* d_rgb[i] = quantise(d_accum[i]); n = number of floats */
 int rtc_quantize_device(int device, const float *d_accum, uint8_t *d_rgb, size_t n, void *stream);
+
+/* Device time of the two render kernels of the LAST rtc_render_device call on this scene that carried
+ * RTC_FLAG_TIME_KERNELS: primary kernel (table preparation + classification + every primary sweep) and path kernel
+ * (bounce rays, shading).  Waits for that render to finish. */
+int rtc_scene_kernel_times(const RtcScene *scene, float *primary_ms, float *paths_ms);
 
 /* number of kernels rtc_render_device launches for this job (for launch accounting) */
 int rtc_render_launch_count(const RtcScene *scene, const RtcDeviceJob *job, int want_ids);

@@ -25,7 +25,7 @@ SPHERE_DTYPE = np.dtype(
     [("pos", "<f4", 3), ("r", "<f4"), ("color", "<f4", 3), ("emissionStrength", "<f4"), ("smoothness", "<f4")])
 
 RTC_SPLIT_TILES, RTC_SPLIT_SAMPLES = 0, 1
-RTC_FLAG_COUNT_EXITS, RTC_FLAG_EXACT_ONLY, RTC_FLAG_PATHS_ONLY, RTC_FLAG_PER_PAIR_FILTER = 1, 2, 4, 8
+RTC_FLAG_COUNT_EXITS, RTC_FLAG_EXACT_ONLY, RTC_FLAG_PATHS_ONLY, RTC_FLAG_PER_PAIR_FILTER, RTC_FLAG_TIME_KERNELS = 1, 2, 4, 8, 16
 STATS_WORDS = 16
 ERRORS = {1: "RTC_ERR_ARG", 2: "RTC_ERR_NO_GPU", 3: "RTC_ERR_CUDA", 4: "RTC_ERR_NCCL", 5: "RTC_ERR_NOMEM"}
 
@@ -88,7 +88,7 @@ _lib = None
 EXPORTS = ["render_cuda", "render_cuda_shutdown", "rtc_camera_look_at", "rtc_normalize", "rtc_device_count",
            "rtc_last_error", "rtc_version", "rtc_scene_create", "rtc_scene_destroy", "rtc_subset_size",
            "rtc_render_device", "rtc_sum_quantize_device", "rtc_quantize_device", "rtc_render_launch_count",
-           "rtc_uninterleave_device", "rtc_fp32_peak_probe", "rtc_scene_update"]
+           "rtc_uninterleave_device", "rtc_fp32_peak_probe", "rtc_scene_update", "rtc_scene_kernel_times", "rtc_synth_scene"]
 
 
 def load_library() -> C.CDLL:
@@ -132,6 +132,10 @@ def load_library() -> C.CDLL:
     lib.rtc_uninterleave_device.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                             C.c_int, C.c_size_t, C.c_void_p]
     lib.rtc_uninterleave_device.restype = C.c_int
+    lib.rtc_scene_kernel_times.argtypes = [C.c_void_p, P(C.c_float), P(C.c_float)]
+    lib.rtc_scene_kernel_times.restype = C.c_int
+    lib.rtc_synth_scene.argtypes = [C.c_uint64, C.c_int32, C.c_void_p]
+    lib.rtc_synth_scene.restype = None
     lib.rtc_fp32_peak_probe.argtypes = [C.c_int, C.c_int, P(C.c_double), P(C.c_double)]
     lib.rtc_fp32_peak_probe.restype = C.c_int
     _lib = lib
@@ -278,6 +282,12 @@ class DeviceScene:
                                                stream or None))
         self.ntris, self.nspheres = len(tris), len(sph)
 
+    def kernel_times(self):
+        """(primary_ms, paths_ms) of the last render launched with RTC_FLAG_TIME_KERNELS (waits for it)."""
+        p, q = C.c_float(), C.c_float()
+        _check(load_library().rtc_scene_kernel_times(self.handle, C.byref(p), C.byref(q)))
+        return p.value, q.value
+
     def launch_count(self, job: DeviceJob, want_ids: bool = False) -> int:
         return load_library().rtc_render_launch_count(self.handle, C.byref(job.to_c()), int(want_ids))
 
@@ -302,6 +312,13 @@ def uninterleave(device: int, d_parts: int, d_img: int, elem_size: int, row_elem
                  band_h: int, part_elems: int, stream: int = 0):
     _check(load_library().rtc_uninterleave_device(device, d_parts, d_img, elem_size, row_elems, height, nparts,
                                                   band_h, part_elems, stream or None))
+
+
+def synth_scene(ntris: int, seed: int = 0xB200) -> np.ndarray:
+    """Triangle[] of BASELINE.json's synthetic config 5 (host code in the library)."""
+    out = np.zeros(ntris, dtype=TRI_DTYPE)
+    load_library().rtc_synth_scene(seed, ntris, out.ctypes.data)
+    return out
 
 
 def fp32_peak_tflops(device: int = 0, reps: int = 5) -> float:

@@ -84,6 +84,8 @@ struct RtcScene {
     int *list = nullptr;          // per-frame work list of primary-hit pixels (sky kernel -> path kernel)
     size_t cap_list = 0;
     float2 *rec = nullptr;        // primary-hit record of each listed pixel
+    cudaEvent_t kev[3] = {nullptr, nullptr, nullptr}; // RTC_FLAG_TIME_KERNELS: before primary, between, after paths
+    bool kev_valid = false;
     unsigned *counters = nullptr; // [0] list length, [1] path-kernel work cursor
 };
 
@@ -122,6 +124,42 @@ void rtc_camera_look_at(const float origin[3], const float lookingAt[3], float f
     out->fov = fov;
 }
 
+// ---- synthetic scene of BASELINE.json's config 5 (the reference has no generator; SURVEY.md 8d defines it) -----
+// splitmix64 stream; per triangle, in this order: centre (3 draws, uniform in [-8,8] x [-6,2] x [-2,14], in front of
+// the reference's default camera), edge vectors e1, e2 (6 draws, uniform in [-0.08,0.08]^3), colour (3 draws,
+// uniform in [0.2,1]), emission (1 draw: 4 for one value in 64, else 0), smoothness (1 draw, uniform in [0,1]).
+// A = c, B = c + e1, C = c + e2 in float; normal = normalized(cross(B - A, C - A)) with the reference's float
+// operations (the rule of raytracing.c:24).  A draw is u = (x >> 11) * 2^-53; value = (float)(lo + (hi - lo) * u).
+void rtc_synth_scene(uint64_t seed, int32_t ntris, Triangle *out)
+{
+    uint64_t state = seed;
+    auto next = [&state]() {
+        uint64_t z = (state += 0x9E3779B97F4A7C15ull);
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        return z ^ (z >> 31);
+    };
+    auto uni = [&next](double lo, double hi) { return (float)(lo + (hi - lo) * ((double)(next() >> 11) * 0x1p-53)); };
+    for (int32_t i = 0; i < ntris; ++i) {
+        Triangle &t = out[i];
+        const float cx = uni(-8, 8), cy = uni(-6, 2), cz = uni(-2, 14);
+        const float e1[3] = {uni(-0.08, 0.08), uni(-0.08, 0.08), uni(-0.08, 0.08)};
+        const float e2[3] = {uni(-0.08, 0.08), uni(-0.08, 0.08), uni(-0.08, 0.08)};
+        t.posA = vec3{cx, cy, cz};
+        t.posB = vec3{cx + e1[0], cy + e1[1], cz + e1[2]};
+        t.posC = vec3{cx + e2[0], cy + e2[1], cz + e2[2]};
+        const float ab[3] = {t.posB.x - t.posA.x, t.posB.y - t.posA.y, t.posB.z - t.posA.z};
+        const float ac[3] = {t.posC.x - t.posA.x, t.posC.y - t.posA.y, t.posC.z - t.posA.z};
+        float n[3], nn[3];
+        host_cross(ab, ac, n);
+        host_normalize(n, nn);
+        t.normal = vec3{nn[0], nn[1], nn[2]};
+        t.mat.color = vec3{uni(0.2, 1), uni(0.2, 1), uni(0.2, 1)};
+        t.mat.emissionStrength = (next() & 63u) == 0 ? 4.0f : 0.0f;
+        t.mat.smoothness = uni(0, 1);
+    }
+}
+
 void rtc_subset_size(int32_t width, int32_t height, const RtcSubset *s, int32_t *out_w, int32_t *out_h)
 {
     int cs = s->col_step > 0 ? s->col_step : 1, rs = s->row_step > 0 ? s->row_step : 1;
@@ -156,6 +194,9 @@ void rtc_scene_destroy(RtcScene *sc)
     cudaFree(sc->list);
     cudaFree(sc->rec);
     cudaFree(sc->counters);
+    for (auto &e : sc->kev)
+        if (e)
+            cudaEventDestroy(e);
     delete sc;
 }
 
@@ -512,6 +553,14 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
             return rc;
         CU(cudaMemsetAsync(msc->counters, 0, 4 * sizeof(unsigned), st));
     }
+    const bool timed = (job->flags & RTC_FLAG_TIME_KERNELS) != 0 && R > 0;
+    msc->kev_valid = false;
+    if (timed) {
+        for (auto &e : msc->kev)
+            if (!e)
+                CU(cudaEventCreate(&e));
+        CU(cudaEventRecord(msc->kev[0], st));
+    }
     if (R > 0) {
         if (sc->ntris > msc->cap_tab || !msc->tab) {
             CU(cudaFree(msc->tab));
@@ -544,7 +593,14 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
                                     (int)bsmem));
             rtc::render_skyblock_kernel<<<bgrid, rtc::SKYB_THREADS, bsmem, st>>>(a, msc->tab, sw);
             CU(cudaGetLastError());
-            return launch_paths(msc, a, msc->list, msc->rec, planes, 0, st);
+            if (timed)
+                CU(cudaEventRecord(msc->kev[1], st));
+            rc = launch_paths(msc, a, msc->list, msc->rec, planes, 0, st);
+            if (timed && !rc) {
+                CU(cudaEventRecord(msc->kev[2], st));
+                msc->kev_valid = true;
+            }
+            return rc;
         }
         size_t smem = rtc::sky_smem_bytes(sc->ntris, sw.stream != 0);
         dim3 fgrid((job->out_w + rtc::FAST_LX * R - 1) / (rtc::FAST_LX * R),
@@ -567,7 +623,14 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
             LAUNCH_SKY(1);
 #undef LAUNCH_SKY
         CU(cudaGetLastError());
-        return launch_paths(msc, a, msc->list, nullptr, planes, 0, st);
+        if (timed)
+            CU(cudaEventRecord(msc->kev[1], st));
+        rc = launch_paths(msc, a, msc->list, nullptr, planes, 0, st);
+        if (timed && !rc) {
+            CU(cudaEventRecord(msc->kev[2], st));
+            msc->kev_valid = true;
+        }
+        return rc;
     }
     if (job->flags & RTC_FLAG_PATHS_ONLY) {
         if (job->maxBounce < 1)
@@ -580,6 +643,22 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
     else
         rtc::render_kernel<false><<<grid, rtc::CTA_THREADS, 0, st>>>(a);
     CU(cudaGetLastError());
+    return RTC_OK;
+}
+
+int rtc_scene_kernel_times(const RtcScene *sc, float *primary_ms, float *paths_ms)
+{
+    if (!sc || !sc->kev_valid)
+        return fail(RTC_ERR_ARG, "kernel_times: the last render of this scene was not launched with RTC_FLAG_TIME_KERNELS");
+    CU(cudaSetDevice(sc->device));
+    CU(cudaEventSynchronize(sc->kev[2]));
+    float a = 0, b = 0;
+    CU(cudaEventElapsedTime(&a, sc->kev[0], sc->kev[1]));
+    CU(cudaEventElapsedTime(&b, sc->kev[1], sc->kev[2]));
+    if (primary_ms)
+        *primary_ms = a;
+    if (paths_ms)
+        *paths_ms = b;
     return RTC_OK;
 }
 
