@@ -130,7 +130,7 @@ struct Lane {
 
 // Shade one closest-hit result; returns true when the PATH (sample) is finished.
 // Restates calcColor's loop body, raytracing.c:270-293.
-__device__ __forceinline__ bool shade(Lane &L, const RenderArgs &a, float best, int bestId)
+__device__ __noinline__ bool shade(Lane &L, const RenderArgs &a, float best, int bestId)
 {
     if (bestId == -1) { // miss: sky, path ends (raytracing.c:289-293)
         f3 env = environment_light(L.dir, a.sky);

@@ -80,14 +80,9 @@ __device__ __forceinline__ void sweep_chunked(const GeoPtr S, int n, int base, b
         const int cn = min(32, n - c0);
         unsigned m = 0;
         if (active) {
-            if (cn == 32) {
-#pragma unroll 8
-                for (int j = 0; j < 32; ++j)
-                    m |= tri_quick(o, d, S[3 * (c0 + j)], S[3 * (c0 + j) + 1], S[3 * (c0 + j) + 2]) ? (1u << j) : 0u;
-            } else {
-                for (int j = 0; j < cn; ++j)
-                    m |= tri_quick(o, d, S[3 * (c0 + j)], S[3 * (c0 + j) + 1], S[3 * (c0 + j) + 2]) ? (1u << j) : 0u;
-            }
+#pragma unroll 4
+            for (int j = 0; j < cn; ++j)
+                m |= tri_quick(o, d, S[3 * (c0 + j)], S[3 * (c0 + j) + 1], S[3 * (c0 + j) + 2]) ? (1u << j) : 0u;
         }
         while (m) {
             const int j = __ffs(m) - 1;
