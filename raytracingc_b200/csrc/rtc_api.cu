@@ -84,6 +84,8 @@ struct RtcScene {
     int *list = nullptr;          // per-frame work list of primary-hit pixels (sky kernel -> path kernel)
     size_t cap_list = 0;
     float2 *rec = nullptr;        // primary-hit record of each listed pixel
+    int4 *btask = nullptr;        // blocks with candidate triangles (block kernel -> block-task kernel)
+    size_t cap_btask = 0;
     cudaEvent_t kev[3] = {nullptr, nullptr, nullptr}; // RTC_FLAG_TIME_KERNELS: before primary, between, after paths
     bool kev_valid = false;
     unsigned *counters = nullptr; // [0] list length, [1] path-kernel work cursor
@@ -193,6 +195,7 @@ void rtc_scene_destroy(RtcScene *sc)
     cudaFree(sc->tab);
     cudaFree(sc->list);
     cudaFree(sc->rec);
+    cudaFree(sc->btask);
     cudaFree(sc->counters);
     for (auto &e : sc->kev)
         if (e)
@@ -397,8 +400,14 @@ int fast_path_R(const RtcScene *sc, const Camera *cam, const RtcDeviceJob *job)
     return R;
 }
 
-int ensure_scratch(RtcScene *sc, size_t npix)
+int ensure_scratch(RtcScene *sc, size_t npix, size_t nbtask = 0)
 {
+    if (nbtask > sc->cap_btask) {
+        CU(cudaFree(sc->btask));
+        sc->btask = nullptr;
+        CU(cudaMalloc(&sc->btask, sizeof(int4) * nbtask));
+        sc->cap_btask = nbtask;
+    }
     if (!sc->counters)
         CU(cudaMalloc(&sc->counters, 4 * sizeof(unsigned)));
     if (npix > sc->cap_list || !sc->list) {
@@ -516,7 +525,7 @@ int rtc_render_launch_count(const RtcScene *sc, const RtcDeviceJob *job, int wan
     (void)want_ids;
     if (!job || job->out_w <= 0 || job->out_h <= 0)
         return 0;
-    return 3; // prepare_primary + sky kernel + path kernel (exact-only modes launch 1)
+    return 4; // prepare_primary + block kernel + block-task kernel + path kernel (other modes launch 1-3)
 }
 
 int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, const RtcDeviceJob *job,
@@ -549,7 +558,9 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
     int R = fast_path_R(sc, cam, job);
     RtcScene *msc = const_cast<RtcScene *>(sc); // per-frame tables and work lists are scratch owned by the handle
     if (R > 0 || (job->flags & RTC_FLAG_PATHS_ONLY)) {
-        if ((rc = ensure_scratch(msc, (size_t)job->out_w * job->out_h)))
+        const size_t nblocks = (size_t)((job->out_w + rtc::BLK_W - 1) / rtc::BLK_W + 8) *
+                               (size_t)((job->out_h + rtc::BLK_H - 1) / rtc::BLK_H + 16) * (size_t)planes;
+        if ((rc = ensure_scratch(msc, (size_t)job->out_w * job->out_h, nblocks)))
             return rc;
         CU(cudaMemsetAsync(msc->counters, 0, 4 * sizeof(unsigned), st));
     }
@@ -581,6 +592,8 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
         sw.list = msc->list;
         sw.list_count = msc->counters;
         sw.rec = msc->rec;
+        sw.btask = msc->btask;
+        sw.btask_count = msc->counters + 2;
         sw.tile = env_int("RTC_SKY_TILE", rtc::SKY_TILE);
         if (sw.tile < 1 || sw.tile > rtc::SKY_TILE)
             sw.tile = rtc::SKY_TILE;
@@ -593,6 +606,25 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
                                     (int)bsmem));
             rtc::render_skyblock_kernel<<<bgrid, rtc::SKYB_THREADS, bsmem, st>>>(a, msc->tab, sw);
             CU(cudaGetLastError());
+            {
+                // remaining samples of the blocks with candidate triangles: persistent warps over a work queue
+                rtc::BlockTaskWork tw;
+                tw.btask = msc->btask;
+                tw.btask_count = msc->counters + 2;
+                tw.cursor = msc->counters + 3;
+                tw.tile = sw.tile;
+                tw.stream = sw.stream;
+                const size_t tsmem = rtc::sky_smem_bytes(sc->ntris, sw.stream != 0);
+                int per_sm = 0;
+                CU(cudaFuncSetAttribute(rtc::render_blocktask_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)tsmem));
+                CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rtc::render_blocktask_kernel,
+                                                                 rtc::BTASK_THREADS, tsmem));
+                if (per_sm < 1)
+                    return fail(RTC_ERR_CUDA, "block-task kernel does not fit on an SM");
+                rtc::render_blocktask_kernel<<<msc->nsm * per_sm, rtc::BTASK_THREADS, tsmem, st>>>(a, msc->tab, tw);
+                CU(cudaGetLastError());
+            }
             if (timed)
                 CU(cudaEventRecord(msc->kev[1], st));
             rc = launch_paths(msc, a, msc->list, msc->rec, planes, 0, st);

@@ -28,6 +28,8 @@ struct SkyWork {
     int *list;            // out: compact indices of primary-hit pixels (nullptr: do not build a list)
     unsigned *list_count; // out: number of entries (zeroed before the launch)
     float2 *rec;          // out (block kernel): {distance, id bits} of each listed pixel's primary hit
+    int4 *btask;          // out (block kernel): blocks to re-sweep per pixel {ci0, cj0, hit mask, plane}
+    unsigned *btask_count;
     int tile;             // triangles per streamed tile (<= SKY_TILE)
     int stream;           // 1: stream the table per sample; 0: resident (needs ntris <= SKY_TILE)
 };

@@ -85,7 +85,8 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
     const int s0 = (int)((long long)g * a.spp / a.nsplit), s1 = (int)((long long)(g + 1) * a.spp / a.nsplit);
     const float wgt = (float)(1.0 / (double)a.spp);
     unsigned hits0 = 0;    // classification: pixels of this block whose primary ray hits
-    unsigned mismatch = 0;
+    bool touched0 = false; // classification: some triangle passed this block's bound
+    unsigned badblocks = 0;
     unsigned long long nrays = 0, nslow = 0, nhit = 0;
     uint32_t k0 = 0;
 
@@ -146,9 +147,15 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
                         const int bits = __float_as_int(e0) | __float_as_int(e1) | __float_as_int(e2) | __float_as_int(e3);
                         mask |= (bits >= 0) ? (1u << j) : 0u;
                     }
-                    if (valid == 0)
+                    if (valid == 0 || touched0)
+                        mask = 0; // a block with candidates at the first sample is re-swept by the block-task kernel
+                    if (s != s0) {
+                        // same rays, same arithmetic: a block without candidates at the first sample has none now
+                        badblocks += mask != 0;
                         mask = 0;
-                    // ---- expand surviving blocks: the warp takes one block at a time, one lane per pixel ----
+                    }
+                    // ---- first sample: expand surviving blocks, the warp takes one block at a time, one lane
+                    //      per pixel ----
                     unsigned pending = __ballot_sync(0xffffffffu, mask != 0);
                     while (pending) {
                         const int src = __ffs(pending) - 1;
@@ -206,7 +213,8 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
             }
         }
         k0 += (uint32_t)ntiles;
-        nrays += __popc(valid);
+        if (s == s0 || !touched0)
+            nrays += __popc(valid);
 
         if (s == s0) {
             // ---- classification: ids are final, hit pixels go to the path kernel's list ----
@@ -250,8 +258,14 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
                 }
             }
             hits0 = hits;
-        } else {
-            mismatch |= hits ^ hits0; // same ray, same arithmetic: every sample must reproduce the classification
+            touched0 = touched;
+            // blocks with candidate triangles: their remaining samples are re-swept pixel by pixel by the
+            // block-task kernel (dynamic work queue: these are the expensive blocks, a tile full of them would
+            // otherwise be one warp's serial work)
+            if (touched && s + 1 < s1 && w.btask != nullptr) {
+                const unsigned pos = atomicAdd(w.btask_count, 1u);
+                w.btask[pos] = make_int4(ci0, cj0, (int)hits, (int)blockIdx.z);
+            }
         }
     }
 
@@ -289,7 +303,7 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
     }
 
     if (a.stats != nullptr) {
-        unsigned long long r_ = nrays, hp = nhit, sl = nslow, bad = __popc(mismatch);
+        unsigned long long r_ = nrays, hp = nhit, sl = nslow, bad = badblocks;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             r_ += __shfl_xor_sync(0xffffffffu, r_, o);
@@ -305,6 +319,178 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
                 atomicAdd(&a.stats[ST_HIT_PIXELS], hp);
             if (bad)
                 atomicAdd(&a.stats[ST_MISMATCH], bad);
+        }
+    }
+}
+
+// ---- block-task kernel: the remaining samples of the blocks that have candidate triangles -------------------
+// Work queue filled by render_skyblock_kernel's classification; persistent warps fetch one (block, plane) task
+// at a time.  The warp owns the block for all its samples: lane p = pixel p (direction computed once), and per
+// sample every triangle is bounded over the block (lane j bounds triangle j of each 32-triangle chunk, the same
+// inequality as above), candidates run the per-pixel edge functions and tri_test_exact in triangle order.  The
+// per-sample result is compared with the classification (it is the same ray); a difference is counted.
+struct BlockTaskWork {
+    const int4 *btask;
+    const unsigned *btask_count;
+    unsigned *cursor;
+    int tile, stream;
+};
+
+constexpr int BTASK_THREADS = 128;
+
+__global__ void __launch_bounds__(BTASK_THREADS) render_blocktask_kernel(const RenderArgs a,
+                                                                         const float4 *__restrict__ tab,
+                                                                         const BlockTaskWork w)
+{
+    extern __shared__ float4 sF[];
+    __shared__ uint64_t bars[2];
+    const int ntris = a.sc.ntris;
+    const bool stream = w.stream != 0;
+    const int tile = stream ? w.tile : (ntris > 0 ? ntris : 1);
+    const int ntiles = (ntris + tile - 1) / tile;
+    const int lane = threadIdx.x & 31;
+    if (!stream) {
+        for (int i = threadIdx.x; i < 4 * ntris; i += BTASK_THREADS)
+            sF[i] = tab[i];
+    } else if (threadIdx.x == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        fence_barrier_init();
+    }
+    __syncthreads();
+    const unsigned ntasks = *w.btask_count;
+    const float fh = (float)(a.H / 2);
+    auto x_of = [&](int ci) { return a.col_start + ci * a.col_step; };
+    auto y_of = [&](int cj) { return a.row_start + (cj / a.band_h) * a.row_step + (cj % a.band_h); };
+    auto dx_at = [&](int ci) { return xdiv((float)(x_of(ci) - a.W / 2), fh); };
+    auto dy_at = [&](int cj) { return xdiv((float)(y_of(cj) - a.H / 2), fh); };
+    auto issue = [&](uint32_t k, int t) {
+        const int n = min(tile, ntris - t * tile);
+        const uint32_t bytes = (uint32_t)n * 4u * (uint32_t)sizeof(float4);
+        fence_proxy_async();
+        mbar_arrive_expect_tx(&bars[k & 1], bytes);
+        tma_load_1d(sF + (size_t)(k & 1) * SKY_TILE * 4, tab + (size_t)t * tile * 4, bytes, &bars[k & 1]);
+    };
+
+    // task state (warp-uniform except the per-pixel values)
+    bool have = false, exhausted = false;
+    int s = 0, s_end = 0;
+    unsigned hits0 = 0;
+    bool pvalid = false;
+    float cx = 0.f, cy = 0.f, dxr = 0.f, dyr = 0.f;
+    f3 d = mk3(0.f, 0.f, 0.f);
+    unsigned long long nrays = 0, nslow = 0, bad = 0;
+    uint32_t k0 = 0;
+
+    while (true) {
+        if (!have && !exhausted) {
+            unsigned t = 0;
+            if (lane == 0)
+                t = atomicAdd(w.cursor, 1u);
+            t = __shfl_sync(0xffffffffu, t, 0);
+            if (t < ntasks) {
+                const int4 bt = w.btask[t];
+                const int ci0 = bt.x, cj0 = bt.y, g = a.split_first + bt.w;
+                hits0 = (unsigned)bt.z;
+                s = (int)((long long)g * a.spp / a.nsplit) + 1; // the first sample was the classification
+                s_end = (int)((long long)(g + 1) * a.spp / a.nsplit);
+                cx = 0.5f * (dx_at(ci0) + dx_at(ci0 + BLK_W - 1));
+                cy = 0.5f * (dy_at(cj0) + dy_at(cj0 + BLK_H - 1));
+                const int ci = ci0 + (lane & 7), cj = cj0 + (lane >> 3);
+                pvalid = ci < a.out_w && cj < a.out_h;
+                dxr = dx_at(ci);
+                dyr = dy_at(cj);
+                d = primary_dir(a, dxr, dyr);
+                have = s < s_end;
+            } else {
+                exhausted = true;
+            }
+        }
+        const bool any = stream ? (__syncthreads_or(have) != 0) : have;
+        if (!any)
+            break;
+        // ---- one sample of this warp's block ----
+        float best = 999999.0f;
+        int id = -1;
+        if (stream && threadIdx.x == 0) {
+            issue(k0, 0);
+            if (ntiles > 1)
+                issue(k0 + 1, 1);
+        }
+        for (int t = 0; t < ntiles; ++t) {
+            const float4 *F = sF;
+            int n = ntris, tbase = 0;
+            if (stream) {
+                const uint32_t k = k0 + (uint32_t)t;
+                mbar_wait(&bars[k & 1], (k >> 1) & 1u);
+                F = sF + (size_t)(k & 1) * SKY_TILE * 4;
+                n = min(tile, ntris - t * tile);
+                tbase = t * tile;
+            }
+            if (have) {
+                for (int c0 = 0; c0 < n; c0 += 32) {
+                    bool bpass = false;
+                    if (c0 + lane < n) {
+                        const float4 *f = F + 4 * (c0 + lane);
+                        const float4 f0 = f[0], f1 = f[1], f2 = f[2], f3_ = f[3];
+                        const float e0 = fmaf(f0.x, cx, fmaf(f0.y, cy, f0.z));
+                        const float e1 = fmaf(f1.x, cx, fmaf(f1.y, cy, f1.z));
+                        const float e2 = fmaf(f2.x, cx, fmaf(f2.y, cy, f2.z));
+                        const float e3 = fmaf(f3_.x, cx, fmaf(f3_.y, cy, f3_.z));
+                        bpass = (__float_as_int(e0) | __float_as_int(e1) | __float_as_int(e2) | __float_as_int(e3)) >= 0;
+                    }
+                    unsigned m = __ballot_sync(0xffffffffu, bpass);
+                    while (m) {
+                        const int j = __ffs(m) - 1;
+                        m &= m - 1;
+                        const int ti = tbase + c0 + j;
+                        const float4 *f = F + 4 * (c0 + j);
+                        const float4 f0 = f[0], f1 = f[1], f2 = f[2], f3_ = f[3];
+                        const float t0 = fmaf(f0.x, dxr, fmaf(f0.y, dyr, f0.w));
+                        const float t1 = fmaf(f1.x, dxr, fmaf(f1.y, dyr, f1.w));
+                        const float t2 = fmaf(f2.x, dxr, fmaf(f2.y, dyr, f2.w));
+                        const float t3 = fmaf(f3_.x, dxr, fmaf(f3_.y, dyr, f3_.w));
+                        const int bits = __float_as_int(t0) | __float_as_int(t1) | __float_as_int(t2) | __float_as_int(t3);
+                        if (bits >= 0 && pvalid) {
+                            unsigned dummy[1];
+                            tri_test_exact<false>(a.origin, d, __ldg(&a.sc.geo[3 * ti]), __ldg(&a.sc.geo[3 * ti + 1]),
+                                                  __ldg(&a.sc.geo[3 * ti + 2]), ti, best, id, dummy);
+                            nslow++;
+                        }
+                    }
+                }
+            }
+            if (stream) {
+                __syncthreads();
+                if (threadIdx.x == 0 && t + 2 < ntiles)
+                    issue(k0 + (uint32_t)t + 2, t + 2);
+            }
+        }
+        k0 += (uint32_t)ntiles;
+        if (have) {
+            const unsigned hm = __ballot_sync(0xffffffffu, id != -1 && pvalid);
+            if (lane == 0)
+                bad += hm != hits0;
+            nrays += pvalid ? 1 : 0;
+            if (++s >= s_end)
+                have = false;
+        }
+    }
+
+    if (a.stats != nullptr) {
+        unsigned long long r_ = nrays, sl = nslow, b_ = bad;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            r_ += __shfl_xor_sync(0xffffffffu, r_, o);
+            sl += __shfl_xor_sync(0xffffffffu, sl, o);
+            b_ += __shfl_xor_sync(0xffffffffu, b_, o);
+        }
+        if (lane == 0 && (r_ | b_)) {
+            atomicAdd(&a.stats[ST_RAYS], r_);
+            atomicAdd(&a.stats[ST_TRI_PAIRS], r_ * (unsigned long long)ntris);
+            atomicAdd(&a.stats[ST_SLOW_PAIRS], sl);
+            if (b_)
+                atomicAdd(&a.stats[ST_MISMATCH], b_);
         }
     }
 }
