@@ -85,6 +85,8 @@ struct RtcScene {
     size_t cap_list = 0;
     float2 *rec = nullptr;        // primary-hit record of each listed pixel
     int4 *btask = nullptr;        // blocks with candidate triangles (block kernel -> block-task kernel)
+    cudaStream_t aux = nullptr;   // the block-task kernel runs here, beside the path kernel
+    cudaEvent_t fork_ev = nullptr, join_ev = nullptr;
     size_t cap_btask = 0;
     cudaEvent_t kev[3] = {nullptr, nullptr, nullptr}; // RTC_FLAG_TIME_KERNELS: before primary, between, after paths
     bool kev_valid = false;
@@ -200,6 +202,12 @@ void rtc_scene_destroy(RtcScene *sc)
     for (auto &e : sc->kev)
         if (e)
             cudaEventDestroy(e);
+    if (sc->fork_ev)
+        cudaEventDestroy(sc->fork_ev);
+    if (sc->join_ev)
+        cudaEventDestroy(sc->join_ev);
+    if (sc->aux)
+        cudaStreamDestroy(sc->aux);
     delete sc;
 }
 
@@ -606,8 +614,17 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
                                     (int)bsmem));
             rtc::render_skyblock_kernel<<<bgrid, rtc::SKYB_THREADS, bsmem, st>>>(a, msc->tab, sw);
             CU(cudaGetLastError());
+            if (timed)
+                CU(cudaEventRecord(msc->kev[1], st));
             {
-                // remaining samples of the blocks with candidate triangles: persistent warps over a work queue
+                // remaining samples of the blocks with candidate triangles: persistent warps over a work queue.
+                // Independent of the path kernel (both only need the classification), so it is forked onto an
+                // auxiliary stream and joined after the path kernel: the two latency-bound kernels share the SMs.
+                if (!msc->aux) {
+                    CU(cudaStreamCreateWithFlags(&msc->aux, cudaStreamNonBlocking));
+                    CU(cudaEventCreateWithFlags(&msc->fork_ev, cudaEventDisableTiming));
+                    CU(cudaEventCreateWithFlags(&msc->join_ev, cudaEventDisableTiming));
+                }
                 rtc::BlockTaskWork tw;
                 tw.btask = msc->btask;
                 tw.btask_count = msc->counters + 2;
@@ -622,12 +639,20 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
                                                                  rtc::BTASK_THREADS, tsmem));
                 if (per_sm < 1)
                     return fail(RTC_ERR_CUDA, "block-task kernel does not fit on an SM");
-                rtc::render_blocktask_kernel<<<msc->nsm * per_sm, rtc::BTASK_THREADS, tsmem, st>>>(a, msc->tab, tw);
+                const bool overlap = env_int("RTC_NO_OVERLAP", 0) == 0;
+                cudaStream_t ts = overlap ? msc->aux : st;
+                if (overlap) {
+                    CU(cudaEventRecord(msc->fork_ev, st));
+                    CU(cudaStreamWaitEvent(msc->aux, msc->fork_ev, 0));
+                }
+                rtc::render_blocktask_kernel<<<msc->nsm * per_sm, rtc::BTASK_THREADS, tsmem, ts>>>(a, msc->tab, tw);
                 CU(cudaGetLastError());
+                if (overlap)
+                    CU(cudaEventRecord(msc->join_ev, msc->aux));
+                rc = launch_paths(msc, a, msc->list, msc->rec, planes, 0, st);
+                if (overlap)
+                    CU(cudaStreamWaitEvent(st, msc->join_ev, 0));
             }
-            if (timed)
-                CU(cudaEventRecord(msc->kev[1], st));
-            rc = launch_paths(msc, a, msc->list, msc->rec, planes, 0, st);
             if (timed && !rc) {
                 CU(cudaEventRecord(msc->kev[2], st));
                 msc->kev_valid = true;

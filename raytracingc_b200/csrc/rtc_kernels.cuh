@@ -130,13 +130,16 @@ struct Lane {
 
 // Shade one closest-hit result; returns true when the PATH (sample) is finished.
 // Restates calcColor's loop body, raytracing.c:270-293.
-__device__ __noinline__ bool shade(Lane &L, const RenderArgs &a, float best, int bestId)
+// miss: sky, the path ends (raytracing.c:289-293)
+__device__ __forceinline__ void shade_miss(Lane &L, const RenderArgs &a)
 {
-    if (bestId == -1) { // miss: sky, path ends (raytracing.c:289-293)
-        f3 env = environment_light(L.dir, a.sky);
-        L.light = xadd3(L.light, xmul3(env, L.tint));
-        return true;
-    }
+    f3 env = environment_light(L.dir, a.sky);
+    L.light = xadd3(L.light, xmul3(env, L.tint));
+}
+
+// hit (bestId != -1): raytracing.c:272-287; returns true when the path is finished
+__device__ __noinline__ bool shade_hit(Lane &L, const RenderArgs &a, float best, int bestId)
+{
     // closest.hitPoint = pos + dir*dst (raytracing.c:238)
     f3 hp = xadd3(L.pos, xscale3(L.dir, best));
     f3 n;
@@ -167,6 +170,15 @@ __device__ __noinline__ bool shade(Lane &L, const RenderArgs &a, float best, int
     L.tint = xscale3(L.tint, xrcp(p));                          // :287
     L.bounce++;
     return L.bounce >= a.maxBounce;                             // loop bound, :268
+}
+
+__device__ __forceinline__ bool shade(Lane &L, const RenderArgs &a, float best, int bestId)
+{
+    if (bestId == -1) {
+        shade_miss(L, a);
+        return true;
+    }
+    return shade_hit(L, a, best, bestId);
 }
 
 // ---- the fused render kernel (exact sweep) ---------------------------------------

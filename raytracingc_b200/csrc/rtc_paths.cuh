@@ -125,8 +125,9 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
     int pix = 0, plane = 0, s_end = 0;
     bool active = false, exhausted = false, first = false, fresh = false;
     const bool has_rec = w.rec != nullptr;
-    float best0 = 999999.0f;
-    int id0 = -1;
+    float best0 = 999999.0f, best = 999999.0f;
+    int id0 = -1, bestId = -1;
+    bool pend = false; // (best, bestId) of the last sweep is a hit that is not shaded yet
     unsigned long long nrays = 0, nhitpix = 0;
     uint32_t k0 = 0; // tiles consumed so far (STREAM): stage = k & 1, parity = (k >> 1) & 1
 
@@ -167,7 +168,9 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
     };
 
     while (true) {
-        // ---- idle lanes fetch the next (pixel, plane) task ----
+        // ---- idle lanes fetch the next (pixel, plane) task; repeated while a lane finishes its pixel in the
+        //      shading pass below, so a warp never leaves (or sweeps with idle lanes) while work is left ----
+        do {
         {
             const bool need = !active && !exhausted;
             const unsigned m = __ballot_sync(0xffffffffu, need);
@@ -217,21 +220,27 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
                 }
             }
         }
-        // ---- known primary hit: shade it without a sweep (the primary kernel sweeps that ray every sample) ----
-        if (has_rec) {
-            while (active && fresh) {
-                fresh = false;
-                if (shade(L, a, best0, id0))
-                    finish_sample();
+        // ---- hit shading, one pass for both kinds of pending hits: the hit the last sweep found, and the known
+        //      primary hit of a lane that starts a sample (the primary kernel sweeps that ray every sample).  A lane
+        //      whose path ends here starts its next sample in the same loop. ----
+        while (active && (pend || (has_rec && fresh))) {
+            if (!pend) {
+                best = best0;
+                bestId = id0;
             }
+            pend = false;
+            fresh = false;
+            if (shade_hit(L, a, best, bestId))
+                finish_sample();
         }
+        } while (__any_sync(0xffffffffu, !active && !exhausted));
         const bool any = STREAM ? (__syncthreads_or(active) != 0) : __any_sync(0xffffffffu, active);
         if (!any)
             break;
 
         // ---- closest hit of the lane's current ray: spheres first, then triangles in order ----
-        float best = 999999.0f;
-        int bestId = -1;
+        best = 999999.0f;
+        bestId = -1;
         if (active)
             for (int k = 0; k < nsph; ++k)
                 sphere_test_exact(L.pos, L.dir, __ldg(&a.sc.s0[k]), k, best, bestId);
@@ -267,8 +276,12 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
                 }
             }
             fresh = false;
-            if (shade(L, a, best, bestId))
+            if (bestId == -1) {
+                shade_miss(L, a);
                 finish_sample();
+            } else {
+                pend = true; // shaded at the top of the next iteration, together with the lanes starting a sample
+            }
         }
     }
 
