@@ -85,6 +85,8 @@ struct RtcScene {
     size_t cap_list = 0;
     float2 *rec = nullptr;        // primary-hit record of each listed pixel
     int4 *btask = nullptr;        // blocks with candidate triangles (block kernel -> block-task kernel)
+    float *sphq = nullptr;        // per-frame sphere bound table (8 floats per sphere)
+    int cap_sphq = 0;
     cudaStream_t aux = nullptr;   // the block-task kernel runs here, beside the path kernel
     cudaEvent_t fork_ev = nullptr, join_ev = nullptr;
     size_t cap_btask = 0;
@@ -198,6 +200,7 @@ void rtc_scene_destroy(RtcScene *sc)
     cudaFree(sc->list);
     cudaFree(sc->rec);
     cudaFree(sc->btask);
+    cudaFree(sc->sphq);
     cudaFree(sc->counters);
     for (auto &e : sc->kev)
         if (e)
@@ -589,14 +592,27 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
         }
         const int nsph_eff = job->trianglesOnly ? 0 : sc->nsph;
         const int bh_ = job->subset.band_h > 0 ? job->subset.band_h : 1;
-        const bool block = nsph_eff == 0 && !(job->flags & RTC_FLAG_PER_PAIR_FILTER) &&
+        const bool block = nsph_eff <= 32 && !(job->flags & RTC_FLAG_PER_PAIR_FILTER) &&
                            (bh_ == 1 || bh_ % rtc::BLK_H == 0) && env_int("RTC_SKY_BLOCK", 1) != 0;
         rtc::PrimaryFrame fr = make_primary_frame(cam, job, R, block);
         if (sc->ntris > 0) {
             rtc::prepare_primary_kernel<<<(sc->ntris + 127) / 128, 128, 0, st>>>(a.sc, fr, msc->tab);
             CU(cudaGetLastError());
         }
+        if (block && nsph_eff > 0) {
+            if (nsph_eff > msc->cap_sphq) {
+                CU(cudaFree(msc->sphq));
+                msc->sphq = nullptr;
+                CU(cudaMalloc(&msc->sphq, sizeof(float) * 8 * (size_t)nsph_eff));
+                msc->cap_sphq = nsph_eff;
+            }
+            rtc::prepare_spheres_kernel<<<(nsph_eff + 31) / 32, 32, 0, st>>>(a.sc, fr, msc->sphq);
+            CU(cudaGetLastError());
+        }
         rtc::SkyWork sw;
+        sw.sphq = msc->sphq;
+        sw.hw = (float)fr.hw;
+        sw.hh = (float)fr.hh;
         sw.list = msc->list;
         sw.list_count = msc->counters;
         sw.rec = msc->rec;

@@ -122,6 +122,54 @@ __global__ void prepare_primary_kernel(const DeviceScene sc, const PrimaryFrame 
         tab[4 * i + k] = out[k];
 }
 
+// ---- spheres: conservative bound of the discriminant over a pixel block ---------------------------------------
+// raySphere (raytracing.c:162-184) rejects a ray when delta = b*b - c < 0, b = off.d, c = off.off - r*r,
+// off = o - centre.  For primary rays d = D/|D| with D affine in (dx, dy), so |D|^2 * delta is the quadratic
+//     Q(dx, dy) = (D.off)^2 - |D|^2 * c = A dx^2 + B dy^2 + C dx dy + E dx + F dy + G ,
+// and over a block centred at (cx, cy) with half extents (hw, hh), by the (exact) second-order Taylor expansion,
+//     max Q <= Q(c) + |Qx(c)| hw + |Qy(c)| hh + |A| hw^2 + |B| hh^2 + |C| hw hh .
+// The table entry holds A, B, C, E, F and G' = G + block term + margins, where the margins bound the reference's
+// float error on delta (41 * 2^-23 * (|off|_1^2 + r^2), scaled by max |D|^2) and this kernel's own evaluation
+// error.  max Q < 0  =>  the reference computes delta < 0 for every pixel of the block  =>  miss.
+__global__ void prepare_spheres_kernel(const DeviceScene sc, const PrimaryFrame fr, float *__restrict__ sphq)
+{
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= sc.nsph)
+        return;
+    const float4 s0 = sc.s0[k];
+    const f3 offf = xsub3(fr.origin, mk3(s0.x, s0.y, s0.z)); // the reference's float subtraction
+    const double off[3] = {offf.x, offf.y, offf.z};
+    const double ex[3] = {fr.ex.x, fr.ex.y, fr.ex.z}, ey[3] = {fr.ey.x, fr.ey.y, fr.ey.z},
+                 ez[3] = {fr.ez.x, fr.ez.y, fr.ez.z};
+    auto dot = [](const double *a, const double *b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; };
+    const double fov = fr.fov, r = s0.w;
+    const double al = dot(ex, off), be = dot(ey, off), ga = fov * dot(ez, off);
+    const double cc = dot(off, off) - r * r;
+    const double A = al * al - dot(ex, ex) * cc, B = be * be - dot(ey, ey) * cc;
+    const double C = 2 * al * be - 2 * dot(ex, ey) * cc;
+    const double E = 2 * al * ga - 2 * fov * dot(ex, ez) * cc, F = 2 * be * ga - 2 * fov * dot(ey, ez) * cc;
+    const double G = ga * ga - fov * fov * dot(ez, ez) * cc;
+    const double X = fr.dxmax, Y = fr.dymax;
+    const double l1 = fabs(off[0]) + fabs(off[1]) + fabs(off[2]);
+    const double u = 1.1920928955078125e-07; // 2^-23
+    const double S = fabs(A) * X * X + fabs(B) * Y * Y + fabs(C) * X * Y + fabs(E) * X + fabs(F) * Y + fabs(G) +
+                     (2 * fabs(A) * X + fabs(C) * Y + fabs(E)) * fr.hw + (2 * fabs(B) * Y + fabs(C) * X + fabs(F)) * fr.hh;
+    const double m_ref = 41.0 * u * (l1 * l1 + r * r) * fr.Dmax * fr.Dmax;
+    const double m_eval = 64.0 * u * S;
+    const double blk = (fabs(A) * fr.hw * fr.hw + fabs(B) * fr.hh * fr.hh + fabs(C) * fr.hw * fr.hh) * 1.000001;
+    float *o = sphq + 8 * k;
+    bool ok = isfinite(A) && isfinite(B) && isfinite(C) && isfinite(E) && isfinite(F) && isfinite(G) && S < 1e30;
+    if (ok) {
+        o[0] = (float)A; o[1] = (float)B; o[2] = (float)C; o[3] = (float)E; o[4] = (float)F;
+        o[5] = __double2float_ru(G + blk + m_ref + m_eval + 1e-30);
+        o[6] = o[7] = 0.f;
+    } else { // cannot reason in float: every block is a candidate
+        o[0] = o[1] = o[2] = o[3] = o[4] = 0.f;
+        o[5] = 1.f;
+        o[6] = o[7] = 0.f;
+    }
+}
+
 // ---- fast render kernel -------------------------------------------------------------
 // Lane layout: 8 x 4 lanes per warp, each lane owns R horizontally adjacent pixels
 // (warp tile 8R x 4); a CTA is 4 warps stacked in y (CTA tile 8R x 16).

@@ -29,6 +29,8 @@ struct SkyWork {
     unsigned *list_count; // out: number of entries (zeroed before the launch)
     float2 *rec;          // out (block kernel): {distance, id bits} of each listed pixel's primary hit
     int4 *btask;          // out (block kernel): blocks to re-sweep per pixel {ci0, cj0, hit mask, plane}
+    const float *sphq;    // block kernel: 8 floats per sphere (prepare_spheres_kernel)
+    float hw, hh;         // block kernel: half extents of a pixel block in (dx, dy), as used for the tables
     unsigned *btask_count;
     int tile;             // triangles per streamed tile (<= SKY_TILE)
     int stream;           // 1: stream the table per sample; 0: resident (needs ntris <= SKY_TILE)

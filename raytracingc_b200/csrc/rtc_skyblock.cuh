@@ -1,4 +1,4 @@
-// rtc_skyblock.cuh -- primary-ray kernel, block form (default when the scene has no spheres).
+// rtc_skyblock.cuh -- primary-ray kernel, block form (the default).
 //
 // Owns EVERY primary ray of the frame: the first sample classifies the pixels (primary-hit pixels go to the path
 // kernel's work list together with their hit record {distance, id}; sky pixels are finished here), and every
@@ -39,6 +39,7 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
     extern __shared__ float4 smem_dyn[];
     __shared__ uint64_t bars[2];
     const int ntris = a.sc.ntris;
+    const int nsph = a.trianglesOnly ? 0 : a.sc.nsph; // <= 32 (host-checked)
     const bool stream = w.stream != 0;
     const int tile = stream ? w.tile : (ntris > 0 ? ntris : 1);
     const int ntiles = (ntris + tile - 1) / tile;
@@ -107,6 +108,51 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
                 issue(k0 + 1, 1);
         }
         const bool warp_busy = __any_sync(0xffffffffu, valid != 0);
+        // ---- spheres come first in the reference's closest-hit loop (raytracing.c:219-228): bound the
+        //      discriminant over the block (prepare_spheres_kernel), expand the blocks a sphere may touch ----
+        if (nsph > 0 && warp_busy) {
+            unsigned smask = 0;
+            for (int k = 0; k < nsph; ++k) {
+                const float *q = w.sphq + 8 * k;
+                const float A = __ldg(q), B = __ldg(q + 1), C = __ldg(q + 2), E = __ldg(q + 3), F_ = __ldg(q + 4),
+                            G = __ldg(q + 5);
+                const float q0 = fmaf(cx, fmaf(A, cx, fmaf(C, cy, E)), fmaf(cy, fmaf(B, cy, F_), G));
+                const float qx = fmaf(2.0f * A, cx, fmaf(C, cy, E)), qy = fmaf(2.0f * B, cy, fmaf(C, cx, F_));
+                const float bound = fmaf(fabsf(qx), w.hw, fmaf(fabsf(qy), w.hh, q0));
+                smask |= !(bound < 0.0f) ? (1u << k) : 0u;
+            }
+            if (valid == 0 || touched0)
+                smask = 0;
+            if (s != s0) {
+                badblocks += smask != 0;
+                smask = 0;
+            }
+            unsigned pending = __ballot_sync(0xffffffffu, smask != 0);
+            while (pending) {
+                const int src = __ffs(pending) - 1;
+                pending &= pending - 1;
+                unsigned m = __shfl_sync(0xffffffffu, smask, src);
+                const int bci0 = __shfl_sync(0xffffffffu, ci0, src), bcj0 = __shfl_sync(0xffffffffu, cj0, src);
+                const unsigned bvalid = __shfl_sync(0xffffffffu, valid, src);
+                const bool mine = (bvalid >> lane) & 1u;
+                const f3 d = primary_dir(a, dx_at(bci0 + (lane & 7)), dy_at(bcj0 + (lane >> 3)));
+                float best = 999999.0f; // the sphere stage is the first to touch a block in a sample
+                int id = -1;
+                while (m) {
+                    const int k = __ffs(m) - 1;
+                    m &= m - 1;
+                    if (mine)
+                        sphere_test_exact(a.origin, d, __ldg(&a.sc.s0[k]), k, best, id);
+                }
+                hitbuf[src * 32 + lane] = make_float2(best, __int_as_float(id));
+                const unsigned hm = __ballot_sync(0xffffffffu, id != -1 && mine);
+                if (lane == src) {
+                    touched = true;
+                    hits = hm;
+                }
+                __syncwarp();
+            }
+        }
         for (int t = 0; t < ntiles; ++t) {
             const float4 *F = sF;
             int n = ntris, tbase = 0;
@@ -314,6 +360,7 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
         if (lane == 0) {
             atomicAdd(&a.stats[ST_RAYS], r_);
             atomicAdd(&a.stats[ST_TRI_PAIRS], r_ * (unsigned long long)ntris);
+            atomicAdd(&a.stats[ST_SPH_PAIRS], r_ * (unsigned long long)nsph);
             atomicAdd(&a.stats[ST_SLOW_PAIRS], sl);
             if (a.ids != nullptr)
                 atomicAdd(&a.stats[ST_HIT_PIXELS], hp);
@@ -345,6 +392,7 @@ __global__ void __launch_bounds__(BTASK_THREADS) render_blocktask_kernel(const R
     extern __shared__ float4 sF[];
     __shared__ uint64_t bars[2];
     const int ntris = a.sc.ntris;
+    const int nsph = a.trianglesOnly ? 0 : a.sc.nsph;
     const bool stream = w.stream != 0;
     const int tile = stream ? w.tile : (ntris > 0 ? ntris : 1);
     const int ntiles = (ntris + tile - 1) / tile;
@@ -412,6 +460,9 @@ __global__ void __launch_bounds__(BTASK_THREADS) render_blocktask_kernel(const R
         // ---- one sample of this warp's block ----
         float best = 999999.0f;
         int id = -1;
+        if (have && pvalid)
+            for (int k = 0; k < nsph; ++k) // spheres first (raytracing.c:219-228)
+                sphere_test_exact(a.origin, d, __ldg(&a.sc.s0[k]), k, best, id);
         if (stream && threadIdx.x == 0) {
             issue(k0, 0);
             if (ntiles > 1)
@@ -488,6 +539,7 @@ __global__ void __launch_bounds__(BTASK_THREADS) render_blocktask_kernel(const R
         if (lane == 0 && (r_ | b_)) {
             atomicAdd(&a.stats[ST_RAYS], r_);
             atomicAdd(&a.stats[ST_TRI_PAIRS], r_ * (unsigned long long)ntris);
+            atomicAdd(&a.stats[ST_SPH_PAIRS], r_ * (unsigned long long)nsph);
             atomicAdd(&a.stats[ST_SLOW_PAIRS], sl);
             if (b_)
                 atomicAdd(&a.stats[ST_MISMATCH], b_);
