@@ -96,3 +96,30 @@ def test_pixel_centre_edges():
         rgb_f, ids_f, st_f = rtc.render(tris, flags=fl, **kw)
         assert (ids_f == ids_e).all() and (rgb_f == rgb_e).all() and st_f["rays"] == st_e["rays"]
     assert (ids_e >= 0).sum() > 100
+
+
+def test_sphere_block_bound_adversarial():
+    """spheres decided by the block bound of the discriminant: many spheres, camera inside one, one behind the
+    camera, sub-pixel and grazing ones -- block kernel == per-pair kernel == exact-only kernel, bit for bit"""
+    import raytracingc_b200 as rtc
+    from raytracingc_b200 import api
+    rng = np.random.default_rng(99)
+    tris = random_scene(rng, 60, 5.0, 1.5)
+    sph = np.zeros(9, dtype=rtc.SPHERE_DTYPE)
+    sph["pos"] = [(0, 1, 0), (-4.75, -1.5, -4.75), (-12, -3, -12), (2, -1, 3), (1.5, -1.2, 2.0), (0.9, -1.2, 1.0),
+                  (3, 0, 8), (-2, -2, 1), (40, 0, 40)]
+    sph["r"] = [2.5, 0.5, 3.0, 0.004, 0.8, 0.05, 4.0, 1e-4, 30.0]
+    sph["color"] = rng.uniform(0.3, 1.0, (9, 3))
+    sph["emissionStrength"] = [0, 0, 0, 5, 0, 2, 0, 0, 0]
+    sph["smoothness"] = rng.uniform(0, 1, 9)
+    for (W, H, origin, look, fov) in [(192, 108, (-4.75, -1.5, -4.75), (0.9, -1.2, 1.0), 1.0),   # inside sphere 1
+                                      (160, 120, (-7.0, -2.0, -7.0), (0.9, -1.2, 1.0), 1.3),
+                                      (129, 67, (0.0, -6.0, 0.5), (0.0, 1.0, 0.0), 0.6)]:
+        cam = rtc.camera_look_at(origin, look, fov)
+        kw = dict(width=W, height=H, spp=3, max_bounce=3, triangles_only=0, camera=cam, want_ids=True, spheres=sph)
+        rgb_e, ids_e, st_e = rtc.render(tris, flags=api.RTC_FLAG_EXACT_ONLY, **kw)
+        for fl in (0, api.RTC_FLAG_PER_PAIR_FILTER, api.RTC_FLAG_PATHS_ONLY):
+            rgb_f, ids_f, st_f = rtc.render(tris, flags=fl, **kw)
+            assert (ids_f == ids_e).all(), f"flags {fl}: {(ids_f != ids_e).sum()} ids differ"
+            assert st_f["rays"] == st_e["rays"] and (rgb_f == rgb_e).all()
+        assert (ids_e < -1).sum() > 0
