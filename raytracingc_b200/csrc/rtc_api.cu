@@ -448,6 +448,7 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
     w.cursor = sc->counters + 1;
     w.planes = planes;
     w.write_ids = write_ids;
+    w.coop = env_int("RTC_NO_COOP", 0) == 0;
     w.tile = env_int("RTC_PATH_TILE", rtc::PATH_TILE);
     if (w.tile < 1 || w.tile > rtc::PATH_TILE)
         w.tile = rtc::PATH_TILE;

@@ -30,6 +30,7 @@ struct PathWork {
     int planes;                 // sub-streams rendered by this launch
     int write_ids;              // 1: this kernel owns the primary-id map (no sky kernel ran)
     int tile;                   // triangles per streamed tile (<= PATH_TILE), STREAM only
+    int coop;                   // 1: cooperative sweep of the last live lanes (0 only for A/B measurements)
     const float2 *rec;          // with a list: {distance, id bits} of each listed pixel's primary hit, found by the
                                 // primary kernel, which also re-sweeps that ray every sample; nullptr: the path
                                 // kernel sweeps primary rays itself
@@ -94,6 +95,31 @@ __device__ __forceinline__ void sweep_chunked(const GeoPtr S, int n, int base, b
     }
 }
 
+// Cooperative sweep for the tail of the work list: when a warp has few live lanes left (and no work to fetch),
+// the 32 lanes form na groups of S lanes; group q sweeps the ray of the q-th live lane, member r testing the
+// triangles j = r, r + S, ... of the tile (exact sequence), and the group's (distance, index) minimum -- lowest
+// index among equal distances, which is what the reference's in-order strict-< scan keeps -- goes back to the
+// owner.  The serial chain of the last pixels (what bounds a frame split over many GPUs) shrinks by ~S.
+struct CoopCtx {
+    int S, r, leader; // group size, member index, lane holding this lane's group result after the reduction
+    bool member;      // this lane's group has a ray
+    f3 o, d;
+    float best;
+    int id;
+};
+
+__device__ __forceinline__ void coop_tile(CoopCtx &c, const float4 *S_, int n, int base)
+{
+    if (!c.member)
+        return;
+    for (int j = c.r; j < n; j += c.S) {
+        if (tri_quick(c.o, c.d, S_[3 * j], S_[3 * j + 1], S_[3 * j + 2])) {
+            unsigned dummy[1];
+            tri_test_exact<false>(c.o, c.d, S_[3 * j], S_[3 * j + 1], S_[3 * j + 2], base + j, c.best, c.id, dummy);
+        }
+    }
+}
+
 template <bool STREAM>
 __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const RenderArgs a, const PathWork w)
 {
@@ -117,6 +143,15 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
 
     const unsigned npix = w.list ? *w.list_count : (unsigned)(a.out_w * a.out_h);
     const unsigned total = npix * (unsigned)w.planes;
+    // Group mode: with fewer tasks than lanes (a frame split over many GPUs, a small image) S lanes share one
+    // pixel.  They hold identical state (same task, same deterministic shading), each sweeps the triangles
+    // j = r, r + S, ... and the group takes the (distance, index) minimum: the pixel's serial chain, which bounds
+    // the kernel when every lane has at most one task, gets ~S times shorter in its sweep part.
+    int S = 1;
+    if (w.coop)
+        while (S < 32 && (unsigned long long)total * (unsigned)(2 * S) <= (unsigned long long)gridDim.x * PATH_THREADS)
+            S *= 2;
+    const int gr = lane & (S - 1), gbase = lane & ~(S - 1);
     const float fh = (float)(a.H / 2);
     const float wgt = (float)(1.0 / (double)a.spp); // main.c:99
 
@@ -145,13 +180,13 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
         L.sample++;
         if (L.sample >= s_end) {
             active = false;
-            if (a.accum != nullptr) {
+            if (a.accum != nullptr && gr == 0) {
                 float *p = a.accum + ((size_t)plane * a.out_w * a.out_h + pix) * 3;
                 p[0] = L.acc.x;
                 p[1] = L.acc.y;
                 p[2] = L.acc.z;
             }
-            if (a.rgb != nullptr && a.nsplit == 1) { // vec3ToColor, raytracing.c:11-15
+            if (a.rgb != nullptr && a.nsplit == 1 && gr == 0) { // vec3ToColor, raytracing.c:11-15
                 uint8_t *p = a.rgb + (size_t)pix * 3;
                 p[0] = (uint8_t)float_to_uint8(L.acc.x);
                 p[1] = (uint8_t)float_to_uint8(L.acc.y);
@@ -172,8 +207,8 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
         //      shading pass below, so a warp never leaves (or sweeps with idle lanes) while work is left ----
         do {
         {
-            const bool need = !active && !exhausted;
-            const unsigned m = __ballot_sync(0xffffffffu, need);
+            const bool need = !active && !exhausted; // identical on the S lanes of a group
+            const unsigned m = __ballot_sync(0xffffffffu, need && gr == 0);
             if (m) {
                 unsigned base = 0;
                 const int leader = __ffs(m) - 1;
@@ -181,7 +216,7 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
                     base = atomicAdd(w.cursor, (unsigned)__popc(m));
                 base = __shfl_sync(0xffffffffu, base, leader);
                 if (need) {
-                    const unsigned t = base + __popc(m & ((1u << lane) - 1u));
+                    const unsigned t = base + __popc(m & ((1u << gbase) - 1u)); // one task per group
                     if (t < total) {
                         plane = (int)(t / npix);
                         pix = w.list ? w.list[t % npix] : (int)(t % npix);
@@ -209,7 +244,7 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
                         }
                         active = L.sample < s_end;
                         if (!active) { // empty sample range: the pixel's partial sum is zero
-                            if (a.accum != nullptr) {
+                            if (a.accum != nullptr && gr == 0) {
                                 float *p = a.accum + ((size_t)plane * a.out_w * a.out_h + pix) * 3;
                                 p[0] = p[1] = p[2] = 0.f;
                             }
@@ -244,8 +279,60 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
         if (active)
             for (int k = 0; k < nsph; ++k)
                 sphere_test_exact(L.pos, L.dir, __ldg(&a.sc.s0[k]), k, best, bestId);
+        // few live lanes and nothing left to fetch: sweep cooperatively (see CoopCtx)
+        const unsigned act = __ballot_sync(0xffffffffu, active);
+        const int na = __popc(act);
+        const bool coop = S == 1 && na > 0 && na <= 16 && w.coop;
+        CoopCtx cc;
+        if (coop) {
+            cc.S = na <= 1 ? 32 : (na <= 2 ? 16 : (na <= 4 ? 8 : (na <= 8 ? 4 : 2)));
+            const int q = lane / cc.S;
+            cc.r = lane % cc.S;
+            cc.member = q < na;
+            const int src = cc.member ? (int)__fns(act, 0, q + 1) : lane;
+            cc.o = mk3(__shfl_sync(0xffffffffu, L.pos.x, src), __shfl_sync(0xffffffffu, L.pos.y, src),
+                       __shfl_sync(0xffffffffu, L.pos.z, src));
+            cc.d = mk3(__shfl_sync(0xffffffffu, L.dir.x, src), __shfl_sync(0xffffffffu, L.dir.y, src),
+                       __shfl_sync(0xffffffffu, L.dir.z, src));
+            cc.best = 999999.0f;
+            cc.id = -1;
+            cc.leader = (int)__popc(act & ((1u << lane) - 1u)) * cc.S; // meaningful on live lanes
+        }
+        auto coop_finish = [&]() {
+            // (distance, index) minimum over each group; all lanes take part in the shuffles
+            for (int o_ = cc.S >> 1; o_ > 0; o_ >>= 1) {
+                const float ob = __shfl_xor_sync(0xffffffffu, cc.best, o_);
+                const int oi = __shfl_xor_sync(0xffffffffu, cc.id, o_);
+                if (oi != -1 && (cc.id == -1 || ob < cc.best || (ob == cc.best && oi < cc.id))) {
+                    cc.best = ob;
+                    cc.id = oi;
+                }
+            }
+            const float gb = __shfl_sync(0xffffffffu, cc.best, cc.leader & 31);
+            const int gi = __shfl_sync(0xffffffffu, cc.id, cc.leader & 31);
+            if (active && gi != -1 && gb < best) { // spheres were tested first by the owner: they win ties
+                best = gb;
+                bestId = gi;
+            }
+        };
+        const bool grouped = S > 1;
+        if (grouped) { // the group's lanes hold the same ray; member gr sweeps every S-th triangle
+            cc.S = S;
+            cc.r = gr;
+            cc.member = active;
+            cc.o = L.pos;
+            cc.d = L.dir;
+            cc.best = 999999.0f;
+            cc.id = -1;
+            cc.leader = lane;
+        }
         if (!STREAM) {
-            sweep_chunked(sGeo, ntris, 0, active, L.pos, L.dir, best, bestId);
+            if (coop || grouped) {
+                coop_tile(cc, sGeo, ntris, 0);
+                coop_finish();
+            } else {
+                sweep_chunked(sGeo, ntris, 0, active, L.pos, L.dir, best, bestId);
+            }
         } else {
             if (threadIdx.x == 0) {
                 issue(k0, 0);
@@ -255,21 +342,26 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
             for (int t = 0; t < ntiles; ++t) {
                 const uint32_t k = k0 + (uint32_t)t;
                 mbar_wait(&bars[k & 1], (k >> 1) & 1u);
-                sweep_chunked(sGeo + (size_t)(k & 1) * PATH_TILE * 3, min(tile, ntris - t * tile), t * tile,
-                              active, L.pos, L.dir, best, bestId);
+                if (coop || grouped)
+                    coop_tile(cc, sGeo + (size_t)(k & 1) * PATH_TILE * 3, min(tile, ntris - t * tile), t * tile);
+                else
+                    sweep_chunked(sGeo + (size_t)(k & 1) * PATH_TILE * 3, min(tile, ntris - t * tile), t * tile,
+                                  active, L.pos, L.dir, best, bestId);
                 __syncthreads(); // every warp is done with this stage
                 if (threadIdx.x == 0 && t + 2 < ntiles)
                     issue(k + 2, t + 2);
             }
             k0 += (uint32_t)ntiles;
+            if (coop || grouped)
+                coop_finish();
         }
 
         // ---- shade (calcColor's loop body), advance the state machine ----
         if (active) {
-            nrays++;
+            nrays += gr == 0;
             if (first) {
                 first = false;
-                if (w.write_ids && plane == 0) {
+                if (w.write_ids && plane == 0 && gr == 0) {
                     if (a.ids != nullptr)
                         a.ids[pix] = bestId;
                     nhitpix += bestId != -1;
