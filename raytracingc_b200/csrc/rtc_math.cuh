@@ -99,7 +99,7 @@ __device__ __forceinline__ float random_value(uint32_t &state) { return rng_to_u
 
 // RandomValueNormalDistrubtion (moremath.c:98-103): all in double, narrowed
 // three times exactly where the reference's `float` locals narrow.
-__device__ __forceinline__ float random_normal(uint32_t &state)
+__device__ __noinline__ float random_normal(uint32_t &state)
 {
     float u1 = random_value(state); // theta's draw comes first
     float u2 = random_value(state);
@@ -124,7 +124,7 @@ struct SkyParams {
 
 // glibc's powf is < 1 ulp; CUDA's powf is several ulp, so evaluate in double
 // and narrow.
-__device__ __forceinline__ float xpowf(float x, float y) { return (float)pow((double)x, (double)y); }
+__device__ __noinline__ float xpowf(float x, float y) { return (float)pow((double)x, (double)y); }
 
 __device__ __noinline__ f3 environment_light(f3 dir, const SkyParams &s)
 {

@@ -21,7 +21,7 @@
 namespace rtc {
 
 constexpr int PATH_THREADS = 128;
-constexpr int PATH_TILE = 1024; // triangles per streamed tile: 48 KB per stage, 2 stages
+constexpr int PATH_TILE = 256; // triangles per streamed tile: 12 KB per stage, 2 stages (occupancy stays register-bound)
 
 struct PathWork {
     const int *list;            // compact pixel indices (cj * out_w + ci) or nullptr = all pixels
@@ -48,8 +48,8 @@ __host__ __device__ inline size_t path_smem_bytes(int ntris, bool stream)
 // the pair is dropped when the reference provably drops it:
 //   * c >= 0                                  (cull, raytracing.c:189)
 //   * |det| < EPS                             (raytracing.c:195; -EPS < det < EPS  <=>  |det| < EPS)
-//   * t = s.h with det's sign;  t < -1e-30 and |det| <= 2^20   =>  u = fl(s.h * fl(1/det)) < 0  (cannot round to -0)
-//   *                           t > |det| * 1.00001              =>  u > 1   (margin >> the 3 roundings of u)
+//   * t = s.h with det's sign;  t < -2^-100 |det|   =>  u = fl(s.h * fl(1/det)) < 0, |u| >= 2^-101: cannot round to -0
+//   *                           t > |det| * 1.00001  =>  u > 1   (margin >> the 3 roundings of u)
 // NaNs never drop a pair (every comparison is written so that an unordered result keeps it).
 // Phase 2: each lane walks the set bits of its survivor mask in index order and runs the reference's full
 // sequence (tri_test_exact) on them, so distances, ties (first index wins) and ids are the reference's.
@@ -64,10 +64,10 @@ __device__ __forceinline__ bool tri_quick(const f3 &o, const f3 &d, const float4
     const float sh = xdot(s, h);
     const float adet = fabsf(det);
     const float t = __int_as_float(__float_as_int(sh) ^ (__float_as_int(det) & 0x80000000)); // s.h * sign(det)
-    const float m = adet * 1.00001f;
-    bool keep = !(adet <= 1048576.0f);    // huge |det| (or NaN): never drop on the negative side
-    keep = keep || !(t < -1e-30f);
-    keep = keep && !(t > m);
+    const float hi = adet * 1.00001f;               // t > hi            =>  u > 1
+    const float lo = adet * -7.8886090522101181e-31f; // t < -2^-100 |det| =>  u < 0 and |u| >= 2^-101: never rounds to -0
+    bool keep = !(t > hi);
+    keep = keep && !(t < lo);
     keep = keep && !(adet < 0.001f);
     keep = keep && !(c >= 0.0f);
     return keep;
