@@ -73,6 +73,33 @@ __device__ __forceinline__ bool tri_quick(const f3 &o, const f3 &d, const float4
     return keep;
 }
 
+// Same decision, folded into the survivor mask: the four compares chain through ONE predicate (FSETP ... .AND P)
+// and a predicated OR sets the bit, instead of four materialised booleans (FSETP + SEL each) and a shifted select.
+template <unsigned BIT>
+__device__ __forceinline__ void tri_quick_bit(const f3 &o, const f3 &d, const float4 &p0, const float4 &p1, const float4 &p2,
+                                              unsigned &m)
+{
+    const f3 n = mk3(p0.w, p1.w, p2.w);
+    const f3 AB = mk3(p1.x, p1.y, p1.z), AC = mk3(p2.x, p2.y, p2.z);
+    const float c = xdot(d, n);
+    const f3 h = xcross(d, AC);
+    const float det = xdot(AB, h);
+    const f3 s = xsub3(o, mk3(p0.x, p0.y, p0.z));
+    const float sh = xdot(s, h);
+    const float adet = fabsf(det);
+    const float t = __int_as_float(__float_as_int(sh) ^ (__float_as_int(det) & 0x80000000));
+    const float hi = adet * 1.00001f;
+    const float lo = adet * -7.8886090522101181e-31f;
+    asm("{\n\t.reg .pred p;\n\t"
+        "setp.leu.f32 p, %1, %2;\n\t"                // !(t > hi)
+        "setp.geu.and.f32 p, %1, %3, p;\n\t"         // !(t < lo)
+        "setp.geu.and.f32 p, %4, 0f3A83126F, p;\n\t" // !(adet < 0.001f)
+        "setp.ltu.and.f32 p, %5, 0f00000000, p;\n\t" // !(c >= 0)
+        "@p or.b32 %0, %0, %6;\n\t}"
+        : "+r"(m)
+        : "f"(t), "f"(hi), "f"(lo), "f"(adet), "f"(c), "n"(BIT));
+}
+
 template <typename GeoPtr>
 __device__ __forceinline__ void sweep_chunked(const GeoPtr S, int n, int base, bool active, const f3 &o, const f3 &d,
                                               float &best, int &bestId)
@@ -81,9 +108,21 @@ __device__ __forceinline__ void sweep_chunked(const GeoPtr S, int n, int base, b
         const int cn = min(32, n - c0);
         unsigned m = 0;
         if (active) {
-#pragma unroll 4
-            for (int j = 0; j < cn; ++j)
-                m |= tri_quick(o, d, S[3 * (c0 + j)], S[3 * (c0 + j) + 1], S[3 * (c0 + j) + 2]) ? (1u << j) : 0u;
+            int j = 0;
+            for (; j + 4 <= cn; j += 4) {
+                const int t0 = 3 * (c0 + j);
+                unsigned m4 = 0;
+                tri_quick_bit<1u>(o, d, S[t0], S[t0 + 1], S[t0 + 2], m4);
+                tri_quick_bit<2u>(o, d, S[t0 + 3], S[t0 + 4], S[t0 + 5], m4);
+                tri_quick_bit<4u>(o, d, S[t0 + 6], S[t0 + 7], S[t0 + 8], m4);
+                tri_quick_bit<8u>(o, d, S[t0 + 9], S[t0 + 10], S[t0 + 11], m4);
+                m |= m4 << j;
+            }
+            for (; j < cn; ++j) {
+                unsigned m1 = 0;
+                tri_quick_bit<1u>(o, d, S[3 * (c0 + j)], S[3 * (c0 + j) + 1], S[3 * (c0 + j) + 2], m1);
+                m |= m1 << j;
+            }
         }
         while (m) {
             const int j = __ffs(m) - 1;
