@@ -45,6 +45,11 @@ extern "C" {
 #define RTC_FLAG_PER_PAIR_FILTER 8u /* primary pre-filter evaluated per (pixel, triangle) pair instead of
                                       per (8x4 pixel block, triangle) + expansion of surviving blocks */
 #define RTC_FLAG_TIME_KERNELS 16u /* record CUDA events around the primary and the path kernel (rtc_scene_kernel_times) */
+#define RTC_FLAG_VERIFY_QUICK 32u /* path kernel: also run the exact test on EVERY (ray, triangle) pair and count in
+                                    device stats word 11 the accepted pairs its conservative quick test had dropped
+                                    (must be 0); needs a stats buffer; slow, for tests */
+#define RTC_FLAG_REF_QUICK 64u  /* path kernel: first phase of the sweep in the reference's own arithmetic (the
+                                   fallback for scenes whose stored normals do not follow the winding) */
 #define RTC_FLAG_PATHS_ONLY 4u  /* no primary pre-filter: every pixel goes through the
                                    path kernel (exact arithmetic, shared-memory tiles) */
 
@@ -61,6 +66,8 @@ typedef struct RenderStats {
     float download_ms;     /* device->host of the image                         */
     int32_t kernels_launched;
     int32_t ngpus_used;
+    uint64_t check_failures; /* device self-checks, must be 0: samples whose primary re-sweep disagreed with the
+                                classification + (RTC_FLAG_VERIFY_QUICK) accepted pairs the quick test had dropped */
 } RenderStats;
 
 /*

@@ -93,6 +93,11 @@ struct RtcScene {
     cudaEvent_t kev[3] = {nullptr, nullptr, nullptr}; // RTC_FLAG_TIME_KERNELS: before primary, between, after paths
     bool kev_valid = false;
     unsigned *counters = nullptr; // [0] list length, [1] path-kernel work cursor
+    float4 *qrec = nullptr;       // quick records of the path kernel's first phase (rtc_paths.cuh), 4 x float4 per triangle
+    int cap_q = 0;
+    float q_obound = 0.f;         // origin bound the records were built for; 0 = not built for the current scene
+    float bound_abs = 0.f;        // max |coordinate| over triangle vertices and sphere extents (host scan at upload)
+    bool quick_ok = false;        // the stored normals follow the winding closely enough for the quick records to pay
 };
 
 extern "C" {
@@ -201,6 +206,7 @@ void rtc_scene_destroy(RtcScene *sc)
     cudaFree(sc->rec);
     cudaFree(sc->btask);
     cudaFree(sc->sphq);
+    cudaFree(sc->qrec);
     cudaFree(sc->counters);
     for (auto &e : sc->kev)
         if (e)
@@ -247,6 +253,37 @@ static int scene_reserve(RtcScene *sc, int ntris, int nsph)
     return RTC_OK;
 }
 
+// Host scan at upload: the coordinate bound the quick records (rtc_paths.cuh) are built for, and whether they pay:
+// a record culls by the sign of d.(AC x AB), which needs the stored normal to be (nearly) parallel to the
+// geometric one; a triangle whose normal is off by more than ~0.25 degree is merely kept more often (never wrong),
+// and a scene with more than 1/16 of such triangles uses the reference-arithmetic quick test instead.
+static void scan_scene(RtcScene *sc, const Triangle *tris, int ntris, const Sphere *spheres, int nsph)
+{
+    float bound = 0.f;
+    long long off = 0;
+    for (int i = 0; i < ntris; ++i) {
+        const float *t = reinterpret_cast<const float *>(&tris[i]);
+        for (int k = 0; k < 9; ++k)
+            bound = std::fmax(bound, std::fabs(t[k]));
+        const double ab[3] = {(double)t[3] - t[0], (double)t[4] - t[1], (double)t[5] - t[2]};
+        const double ac[3] = {(double)t[6] - t[0], (double)t[7] - t[1], (double)t[8] - t[2]};
+        const double N[3] = {ac[1] * ab[2] - ac[2] * ab[1], ac[2] * ab[0] - ac[0] * ab[2], ac[0] * ab[1] - ac[1] * ab[0]};
+        const double nn = t[9] * N[0] + t[10] * N[1] + t[11] * N[2], NN = N[0] * N[0] + N[1] * N[1] + N[2] * N[2];
+        const double n2 = (double)t[9] * t[9] + (double)t[10] * t[10] + (double)t[11] * t[11];
+        // sin^2 of the angle between n and N: 1 - (n.N)^2 / (|n|^2 |N|^2)
+        if (!(NN > 0.0) || !(n2 > 0.0) || !(1.0 - nn * nn / (NN * n2) < 2e-5))
+            ++off;
+    }
+    for (int i = 0; i < nsph; ++i) {
+        const float *t = reinterpret_cast<const float *>(&spheres[i]);
+        for (int k = 0; k < 3; ++k)
+            bound = std::fmax(bound, std::fabs(t[k]) + std::fabs(t[3]));
+    }
+    sc->bound_abs = bound;
+    sc->quick_ok = off * 16 <= (long long)ntris;
+    sc->q_obound = 0.f;
+}
+
 // copy the caller's AoS arrays to the device and flatten them there (one-shot kernels), on `st`
 static int scene_upload(RtcScene *sc, const Triangle *tris, int ntris, const Sphere *spheres, int nsph,
                         cudaStream_t st)
@@ -256,6 +293,7 @@ static int scene_upload(RtcScene *sc, const Triangle *tris, int ntris, const Sph
         return rc;
     sc->ntris = ntris;
     sc->nsph = nsph;
+    scan_scene(sc, tris, ntris, spheres, nsph);
     float *raw_t = sc->raw;
     float *raw_s = reinterpret_cast<float *>(reinterpret_cast<char *>(sc->raw) +
                                              sizeof(Triangle) * (size_t)(ntris > 0 ? ntris : 1));
@@ -439,9 +477,38 @@ int ensure_scratch(RtcScene *sc, size_t npix, size_t nbtask = 0)
 
 // the path kernel: persistent grid over a work list (list == nullptr: every pixel of the subset)
 int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const float2 *rec, int planes, int write_ids,
-                 cudaStream_t st)
+                 unsigned flags, cudaStream_t st)
 {
     rtc::PathWork w;
+    // phase 1 of the sweep: quick records (1), + verification against the exact test (2), or the reference's arithmetic (0)
+    const bool ref_quick = (flags & RTC_FLAG_REF_QUICK) != 0 || env_int("RTC_REF_QUICK", 0) != 0;
+    const int mode = ref_quick ? 0 : ((flags & RTC_FLAG_VERIFY_QUICK) ? 2 : (sc->quick_ok ? 1 : 0));
+    if (mode == 2 && !a.stats)
+        return fail(RTC_ERR_ARG, "RTC_FLAG_VERIFY_QUICK needs a stats buffer");
+    w.qrec = nullptr;
+    w.obound = 0.f;
+    if (mode != 0) {
+        // bounce rays start on the scene's surfaces; only when this kernel sweeps the primary rays too does the camera count
+        float need = sc->bound_abs;
+        if (!rec)
+            need = std::fmax(need, std::fmax(std::fabs(a.origin.x), std::fmax(std::fabs(a.origin.y), std::fabs(a.origin.z))));
+        need = need * 1.001f + 1e-6f;
+        if (sc->ntris > sc->cap_q || !sc->qrec) {
+            cudaFree(sc->qrec);
+            sc->qrec = nullptr;
+            CU(cudaMalloc(&sc->qrec, sizeof(float4) * 4 * (size_t)(sc->ntris > 0 ? sc->ntris : 1)));
+            sc->cap_q = sc->ntris > 0 ? sc->ntris : 1;
+            sc->q_obound = 0.f;
+        }
+        if (!(need <= sc->q_obound) && sc->ntris > 0) {
+            const float ob = need * 1.25f;
+            rtc::quick_records_kernel<<<(sc->ntris + 127) / 128, 128, 0, st>>>(sc->geo, sc->ntris, ob, sc->qrec);
+            CU(cudaGetLastError());
+            sc->q_obound = ob;
+        }
+        w.qrec = sc->qrec;
+        w.obound = sc->q_obound;
+    }
     w.list = list;
     w.rec = rec;
     w.list_count = sc->counters;
@@ -452,26 +519,23 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
     w.tile = env_int("RTC_PATH_TILE", rtc::PATH_TILE);
     if (w.tile < 1 || w.tile > rtc::PATH_TILE)
         w.tile = rtc::PATH_TILE;
-    const size_t resident = rtc::path_smem_bytes(sc->ntris, false);
+    const size_t resident = rtc::path_smem_bytes(sc->ntris, false, mode);
     const bool stream = env_int("RTC_FORCE_STREAM", 0) != 0 || resident > 96 * 1024;
-    const size_t smem = rtc::path_smem_bytes(sc->ntris, stream);
+    const size_t smem = rtc::path_smem_bytes(sc->ntris, stream, mode);
     int per_sm = 0;
-    if (stream) {
-        CU(cudaFuncSetAttribute(rtc::render_paths_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rtc::render_paths_kernel<true>, rtc::PATH_THREADS, smem));
-    } else {
-        CU(cudaFuncSetAttribute(rtc::render_paths_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rtc::render_paths_kernel<false>, rtc::PATH_THREADS, smem));
-    }
+    using PathKernel = void (*)(const rtc::RenderArgs, const rtc::PathWork);
+    static const PathKernel kernels[2][3] = {
+        {rtc::render_paths_kernel<false, 0>, rtc::render_paths_kernel<false, 1>, rtc::render_paths_kernel<false, 2>},
+        {rtc::render_paths_kernel<true, 0>, rtc::render_paths_kernel<true, 1>, rtc::render_paths_kernel<true, 2>}};
+    const PathKernel kern = kernels[stream ? 1 : 0][mode];
+    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, rtc::PATH_THREADS, smem));
     if (per_sm < 1)
         return fail(RTC_ERR_CUDA, "path kernel does not fit on an SM (smem %zu)", smem);
     long long tasks = (long long)a.out_w * a.out_h * planes; // upper bound when a list is used
     long long want = (tasks + rtc::PATH_THREADS - 1) / rtc::PATH_THREADS;
     int blocks = (int)std::min<long long>((long long)sc->nsm * per_sm, want > 0 ? want : 1);
-    if (stream)
-        rtc::render_paths_kernel<true><<<blocks, rtc::PATH_THREADS, smem, st>>>(a, w);
-    else
-        rtc::render_paths_kernel<false><<<blocks, rtc::PATH_THREADS, smem, st>>>(a, w);
+    kern<<<blocks, rtc::PATH_THREADS, smem, st>>>(a, w);
     CU(cudaGetLastError());
     return RTC_OK;
 }
@@ -666,7 +730,7 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
                 CU(cudaGetLastError());
                 if (overlap)
                     CU(cudaEventRecord(msc->join_ev, msc->aux));
-                rc = launch_paths(msc, a, msc->list, msc->rec, planes, 0, st);
+                rc = launch_paths(msc, a, msc->list, msc->rec, planes, 0, job->flags, st);
                 if (overlap)
                     CU(cudaStreamWaitEvent(st, msc->join_ev, 0));
             }
@@ -699,7 +763,7 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
         CU(cudaGetLastError());
         if (timed)
             CU(cudaEventRecord(msc->kev[1], st));
-        rc = launch_paths(msc, a, msc->list, nullptr, planes, 0, st);
+        rc = launch_paths(msc, a, msc->list, nullptr, planes, 0, job->flags, st);
         if (timed && !rc) {
             CU(cudaEventRecord(msc->kev[2], st));
             msc->kev_valid = true;
@@ -709,7 +773,7 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
     if (job->flags & RTC_FLAG_PATHS_ONLY) {
         if (job->maxBounce < 1)
             return fail(RTC_ERR_ARG, "RTC_FLAG_PATHS_ONLY needs maxBounce >= 1");
-        return launch_paths(msc, a, nullptr, nullptr, planes, 1, st);
+        return launch_paths(msc, a, nullptr, nullptr, planes, 1, job->flags, st);
     }
     dim3 grid((job->out_w + rtc::CTA_W - 1) / rtc::CTA_W, (job->out_h + rtc::CTA_H - 1) / rtc::CTA_H, planes);
     if (job->flags & RTC_FLAG_COUNT_EXITS)
@@ -1096,6 +1160,7 @@ int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const
         for (int e = 0; e < 6; ++e)
             st->tri_exit[e] = tot[rtc::ST_EXIT0 + e];
         st->hit_pixels = tot[rtc::ST_HIT_PIXELS];
+        st->check_failures = tot[rtc::ST_MISMATCH];
         st->upload_ms = up_ms;
         st->kernel_ms = k_ms;
         float gms = 0;

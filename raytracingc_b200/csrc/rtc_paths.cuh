@@ -9,7 +9,8 @@
 // Work list: either the compact list of primary-hit pixels produced by the sky kernel (rtc_sky.cuh), or, with
 // list == nullptr, every pixel of the subset.  A task is (pixel, plane); plane = sub-stream of a sample split.
 //
-// Geometry (48 B per triangle, rtc_scene.cuh) lives in shared memory:
+// Per-triangle data of the sweep's first phase lives in shared memory -- MODE 0: the geometry itself (48 B per
+// triangle, rtc_scene.cuh); MODE 1/2: the 64 B quick records (QuickRecord below):
 //   STREAM = false  the whole scene is resident (loaded once per CTA); warps run independently.
 //   STREAM = true   scenes of any size: PATH_TILE-triangle tiles are streamed by the TMA unit
 //                   (cp.async.bulk + mbarrier, double-buffered); the CTA's warps sweep in lock-step.
@@ -31,14 +32,20 @@ struct PathWork {
     int write_ids;              // 1: this kernel owns the primary-id map (no sky kernel ran)
     int tile;                   // triangles per streamed tile (<= PATH_TILE), STREAM only
     int coop;                   // 1: cooperative sweep of the last live lanes (0 only for A/B measurements)
+    const float4 *qrec;         // MODE >= 1: quick records (4 x float4 per triangle), built by quick_records_kernel
+    float obound;               // MODE >= 1: the records are valid for ray origins with max |o_i| <= obound
     const float2 *rec;          // with a list: {distance, id bits} of each listed pixel's primary hit, found by the
                                 // primary kernel, which also re-sweeps that ray every sample; nullptr: the path
                                 // kernel sweeps primary rays itself
 };
 
-__host__ __device__ inline size_t path_smem_bytes(int ntris, bool stream)
+// float4 per triangle in shared memory: geometry (MODE 0) or quick record (MODE 1, 2)
+__host__ __device__ constexpr int path_rec_f4(int mode) { return mode == 0 ? 3 : 4; }
+
+__host__ __device__ inline size_t path_smem_bytes(int ntris, bool stream, int mode)
 {
-    return stream ? (size_t)2 * PATH_TILE * 3 * sizeof(float4) : (size_t)(ntris > 0 ? ntris : 1) * 3 * sizeof(float4);
+    const size_t rs = (size_t)path_rec_f4(mode) * sizeof(float4);
+    return stream ? (size_t)2 * PATH_TILE * rs : (size_t)(ntris > 0 ? ntris : 1) * rs;
 }
 
 // The reference's ray-triangle test arranged for SIMT, in two phases per chunk of 32 triangles.
@@ -100,45 +107,205 @@ __device__ __forceinline__ void tri_quick_bit(const f3 &o, const f3 &d, const fl
         : "f"(t), "f"(hi), "f"(lo), "f"(adet), "f"(c), "n"(BIT));
 }
 
-template <typename GeoPtr>
-__device__ __forceinline__ void sweep_chunked(const GeoPtr S, int n, int base, bool active, const f3 &o, const f3 &d,
-                                              float &best, int &bestId)
+// ---- MODE 1: conservative quick test from per-triangle quick records ----------------------------------------
+//
+// Phase 1 does not have to use the reference's arithmetic -- it only has to keep every pair the reference
+// accepts; phase 2 (tri_test_exact, in index order) produces the result.  With w = s x d (s = o - A):
+//     s.(d x AC) = AC.w        d.(s x AB) = -AB.w        AB.(d x AC) = d.(AC x AB)
+// so the numerators of u and v and the determinant cost 20 FMA-pipe operations per pair (the reference's u alone
+// costs 29), and the test sees the whole triangle, not only the u strip.  The values differ from the reference's
+// floats by rounding only; mu (per triangle, built in double by quick_records_kernel) bounds
+// |reference's float - exact| + |this code's float - exact| for every ray with max|d_i| <= QUICK_DBOUND and
+// max|o_i| <= obound (other rays skip phase 1: all pairs go to phase 2):
+//     |sh_r - U|, |vn_r - V| <= 2^-17 (obound + max|A_i|) Dmax Emax        (73 u S Dmax Emax, u = 2^-24)
+//     |det_r - det|          <= 2^-18 Dmax Emax^2                           (55 u), Emax = max |AB_i|, |AC_i|
+// The record holds the edges and N = AC x AB multiplied by f = +-1 so that "det~ > 0" means "front facing by the
+// stored normal" (n = lambda N + e, lambda and e computed in double; f = -sign(lambda)).  A pair is dropped when
+//   det~ < thr      det~ <= -X: c_r = fl(d.n) >= 0 (cull, raytracing.c:189), X = mu + Dmax (2^-19 nmax + 3 emax)/|lambda|;
+//                   |det~| < EPS - mu: |det_r| < EPS (raytracing.c:195).  thr = EPS - mu if X + mu < EPS, else -X
+//   det~ > mu (the sign of det_r is known) and one of
+//     U~ < -mu          u_r < 0  (mu >= 1e-18 keeps fl(sh_r * inv_r) away from -0)
+//     V~ < -mu          v_r < 0
+//     U~ + V~ > det~ (1 + 2^-19) + 4 mu      then u_r > 1, or fl(u_r + v_r) > 1 (u_r, v_r >= 0 carry <= 2.01 u each)
+// Every comparison keeps the pair when unordered (NaN) and degenerate triangles get mu = inf, thr = -inf.
+constexpr float QUICK_DBOUND = 1.0625f;
+
+__global__ void quick_records_kernel(const float4 *__restrict__ geo, int n, float obound, float4 *__restrict__ q)
 {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+        return;
+    const float4 g0 = geo[3 * i], g1 = geo[3 * i + 1], g2 = geo[3 * i + 2];
+    const double ab[3] = {g1.x, g1.y, g1.z}, ac[3] = {g2.x, g2.y, g2.z}, nr[3] = {g0.w, g1.w, g2.w};
+    const double N[3] = {ac[1] * ab[2] - ac[2] * ab[1], ac[2] * ab[0] - ac[0] * ab[2], ac[0] * ab[1] - ac[1] * ab[0]};
+    const double nn = nr[0] * N[0] + nr[1] * N[1] + nr[2] * N[2];
+    const double NN = N[0] * N[0] + N[1] * N[1] + N[2] * N[2];
+    const double Em = fmax(fmax(fmax(fabs(ab[0]), fabs(ab[1])), fabs(ab[2])), fmax(fmax(fabs(ac[0]), fabs(ac[1])), fabs(ac[2])));
+    const double At = fmax(fmax(fabs((double)g0.x), fabs((double)g0.y)), fabs((double)g0.z));
+    const double nm = fmax(fmax(fabs(nr[0]), fabs(nr[1])), fabs(nr[2]));
+    const double inf = __longlong_as_double(0x7ff0000000000000LL);
+    const double Db = (double)QUICK_DBOUND;
+    double mu = inf, thr = -inf, f = 1.0;
+    // written so that NaN or inf anywhere leaves mu = inf, thr = -inf (the pair always goes to phase 2)
+    if (NN > 0.0 && NN < 1e40 && Em < 1e10 && At < 1e10 && nm < 1e10 && (double)obound < 1e10) {
+        const double lam = nn / NN;
+        const double e0 = nr[0] - lam * N[0], e1 = nr[1] - lam * N[1], e2 = nr[2] - lam * N[2];
+        const double em = fmax(fmax(fabs(e0), fabs(e1)), fabs(e2)) * (1.0 + 1e-9) + 1e-12 * nm;
+        f = lam < 0.0 ? 1.0 : -1.0;
+        const double m = fmax(0x1p-17 * ((double)obound + At) * Db * Em, 0x1p-18 * Db * Em * Em) * 1.01 + 1e-18;
+        const double alam = fabs(lam);
+        const double X = alam > 0.0 ? m + Db * (0x1p-19 * nm + 3.0 * em + 1e-30) / alam * 1.01 : inf;
+        const double EPSq = 0.0009999;
+        mu = m;
+        thr = (X + m < EPSq) ? EPSq - m : -X;
+    }
+    const float fs = (float)f;
+    q[4 * i + 0] = make_float4(g0.x, g0.y, g0.z, __double2float_ru(mu));
+    q[4 * i + 1] = make_float4(-fs * g1.x, -fs * g1.y, -fs * g1.z, __double2float_rd(thr));
+    q[4 * i + 2] = make_float4(fs * g2.x, fs * g2.y, fs * g2.z, __double2float_ru(4.0 * mu));
+    q[4 * i + 3] = make_float4(fs * (float)N[0], fs * (float)N[1], fs * (float)N[2], 0.0f);
+}
+
+// the values of the quick test for one pair (see above); FMUL + FFMA chains, no attempt to match the reference's rounding
+struct QuickVals {
+    float U, V, det, sum, hi, mu, thr;
+};
+__device__ __forceinline__ QuickVals quick_vals(const f3 &o, const f3 &d, const float4 &r0, const float4 &r1, const float4 &r2,
+                                                const float4 &r3)
+{
+    QuickVals v;
+    const float sx = o.x - r0.x, sy = o.y - r0.y, sz = o.z - r0.z;
+    const float wx = fmaf(sy, d.z, -(sz * d.y)), wy = fmaf(sz, d.x, -(sx * d.z)), wz = fmaf(sx, d.y, -(sy * d.x));
+    v.U = fmaf(r2.z, wz, fmaf(r2.y, wy, r2.x * wx));
+    v.V = fmaf(r1.z, wz, fmaf(r1.y, wy, r1.x * wx));
+    v.det = fmaf(r3.z, d.z, fmaf(r3.y, d.y, r3.x * d.x));
+    v.sum = v.U + v.V;
+    v.hi = fmaf(v.det, 1.0000019073486328f, r2.w);
+    v.mu = r0.w;
+    v.thr = r1.w;
+    return v;
+}
+
+__device__ __forceinline__ bool tri_quick2(const f3 &o, const f3 &d, const float4 &r0, const float4 &r1, const float4 &r2,
+                                           const float4 &r3)
+{
+    const QuickVals v = quick_vals(o, d, r0, r1, r2, r3);
+    bool p = !(v.U < -v.mu);
+    p = p && !(v.V < -v.mu);
+    p = p && !(v.sum > v.hi);
+    p = p || !(v.det > v.mu);
+    p = p && !(v.det < v.thr);
+    return p;
+}
+
+template <unsigned BIT>
+__device__ __forceinline__ void tri_quick2_bit(const f3 &o, const f3 &d, const float4 &r0, const float4 &r1, const float4 &r2,
+                                               const float4 &r3, unsigned &m)
+{
+    const QuickVals v = quick_vals(o, d, r0, r1, r2, r3);
+    const float nmu = -v.mu;
+    asm("{\n\t.reg .pred p;\n\t"
+        "setp.geu.f32 p, %1, %2;\n\t"        // !(U < -mu)
+        "setp.geu.and.f32 p, %3, %2, p;\n\t" // !(V < -mu)
+        "setp.leu.and.f32 p, %4, %5, p;\n\t" // !(U + V > hi)
+        "setp.leu.or.f32 p, %6, %7, p;\n\t"  // or the sign of det is not known: !(det > mu)
+        "setp.geu.and.f32 p, %6, %8, p;\n\t" // !(det < thr)
+        "@p or.b32 %0, %0, %9;\n\t}"
+        : "+r"(m)
+        : "f"(v.U), "f"(nmu), "f"(v.V), "f"(v.sum), "f"(v.hi), "f"(v.det), "f"(v.mu), "f"(v.thr), "n"(BIT));
+}
+
+// a ray the quick records are valid for (see above); other rays send every pair to phase 2
+__device__ __forceinline__ bool quick_ray_ok(const f3 &o, const f3 &d, float obound)
+{
+    const float dm = fmaxf(fmaxf(fabsf(d.x), fabsf(d.y)), fabsf(d.z));
+    const float om = fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z));
+    return dm <= QUICK_DBOUND && om <= obound; // false for NaN
+}
+
+// MODE 0: S = geometry tile (3 float4 per triangle), quick test in the reference's arithmetic.
+// MODE 1: S = quick-record tile (4 float4 per triangle); phase 2 reads the geometry through the read-only cache.
+// MODE 2: MODE 1 + every pair also runs the exact test; an accepted pair the quick test dropped is counted (viol).
+template <int MODE>
+__device__ __forceinline__ void sweep_chunked(const float4 *S, const float4 *__restrict__ geo, float obound, int n, int base,
+                                              bool active, const f3 &o, const f3 &d, float &best, int &bestId,
+                                              unsigned &viol)
+{
+    const bool rayok = MODE == 0 || quick_ray_ok(o, d, obound);
     for (int c0 = 0; c0 < n; c0 += 32) {
         const int cn = min(32, n - c0);
         unsigned m = 0;
         if (active) {
-            int j = 0;
-            for (; j + 4 <= cn; j += 4) {
-                const int t0 = 3 * (c0 + j);
-                unsigned m4 = 0;
-                tri_quick_bit<1u>(o, d, S[t0], S[t0 + 1], S[t0 + 2], m4);
-                tri_quick_bit<2u>(o, d, S[t0 + 3], S[t0 + 4], S[t0 + 5], m4);
-                tri_quick_bit<4u>(o, d, S[t0 + 6], S[t0 + 7], S[t0 + 8], m4);
-                tri_quick_bit<8u>(o, d, S[t0 + 9], S[t0 + 10], S[t0 + 11], m4);
-                m |= m4 << j;
+            if (!rayok) {
+                m = cn == 32 ? 0xffffffffu : (1u << cn) - 1u;
+            } else if (MODE == 0) {
+                int j = 0;
+                for (; j + 4 <= cn; j += 4) {
+                    const int t0 = 3 * (c0 + j);
+                    unsigned m4 = 0;
+                    tri_quick_bit<1u>(o, d, S[t0], S[t0 + 1], S[t0 + 2], m4);
+                    tri_quick_bit<2u>(o, d, S[t0 + 3], S[t0 + 4], S[t0 + 5], m4);
+                    tri_quick_bit<4u>(o, d, S[t0 + 6], S[t0 + 7], S[t0 + 8], m4);
+                    tri_quick_bit<8u>(o, d, S[t0 + 9], S[t0 + 10], S[t0 + 11], m4);
+                    m |= m4 << j;
+                }
+                for (; j < cn; ++j) {
+                    unsigned m1 = 0;
+                    tri_quick_bit<1u>(o, d, S[3 * (c0 + j)], S[3 * (c0 + j) + 1], S[3 * (c0 + j) + 2], m1);
+                    m |= m1 << j;
+                }
+            } else {
+                int j = 0;
+                for (; j + 4 <= cn; j += 4) {
+                    const float4 *R = S + 4 * (c0 + j);
+                    unsigned m4 = 0;
+                    tri_quick2_bit<1u>(o, d, R[0], R[1], R[2], R[3], m4);
+                    tri_quick2_bit<2u>(o, d, R[4], R[5], R[6], R[7], m4);
+                    tri_quick2_bit<4u>(o, d, R[8], R[9], R[10], R[11], m4);
+                    tri_quick2_bit<8u>(o, d, R[12], R[13], R[14], R[15], m4);
+                    m |= m4 << j;
+                }
+                for (; j < cn; ++j) {
+                    const float4 *R = S + 4 * (c0 + j);
+                    unsigned m1 = 0;
+                    tri_quick2_bit<1u>(o, d, R[0], R[1], R[2], R[3], m1);
+                    m |= m1 << j;
+                }
             }
-            for (; j < cn; ++j) {
-                unsigned m1 = 0;
-                tri_quick_bit<1u>(o, d, S[3 * (c0 + j)], S[3 * (c0 + j) + 1], S[3 * (c0 + j) + 2], m1);
-                m |= m1 << j;
+        }
+        if (MODE == 2 && active) {
+            for (int j = 0; j < cn; ++j) {
+                const int i = base + c0 + j;
+                unsigned ex[6] = {0, 0, 0, 0, 0, 0};
+                float b_ = 999999.0f;
+                int id_ = -1;
+                tri_test_exact<true>(o, d, __ldg(&geo[3 * i]), __ldg(&geo[3 * i + 1]), __ldg(&geo[3 * i + 2]), i, b_, id_, ex);
+                if (ex[5] && !((m >> j) & 1u))
+                    viol++;
             }
         }
         while (m) {
             const int j = __ffs(m) - 1;
             m &= m - 1;
             unsigned dummy[1];
-            tri_test_exact<false>(o, d, S[3 * (c0 + j)], S[3 * (c0 + j) + 1], S[3 * (c0 + j) + 2], base + c0 + j, best,
-                                  bestId, dummy);
+            if (MODE == 0) {
+                tri_test_exact<false>(o, d, S[3 * (c0 + j)], S[3 * (c0 + j) + 1], S[3 * (c0 + j) + 2], base + c0 + j, best,
+                                      bestId, dummy);
+            } else {
+                const int i = base + c0 + j;
+                tri_test_exact<false>(o, d, __ldg(&geo[3 * i]), __ldg(&geo[3 * i + 1]), __ldg(&geo[3 * i + 2]), i, best, bestId,
+                                      dummy);
+            }
         }
     }
 }
 
 // Cooperative sweep for the tail of the work list: when a warp has few live lanes left (and no work to fetch),
 // the 32 lanes form na groups of S lanes; group q sweeps the ray of the q-th live lane, member r testing the
-// triangles j = r, r + S, ... of the tile (exact sequence), and the group's (distance, index) minimum -- lowest
-// index among equal distances, which is what the reference's in-order strict-< scan keeps -- goes back to the
-// owner.  The serial chain of the last pixels (what bounds a frame split over many GPUs) shrinks by ~S.
+// triangles j = r, r + S, ... of the tile (quick test, then the exact sequence), and the group's (distance, index)
+// minimum -- lowest index among equal distances, which is what the reference's in-order strict-< scan keeps --
+// goes back to the owner.  The serial chain of the last pixels (what bounds a frame split over many GPUs)
+// shrinks by ~S.
 struct CoopCtx {
     int S, r, leader; // group size, member index, lane holding this lane's group result after the reduction
     bool member;      // this lane's group has a ray
@@ -147,22 +314,34 @@ struct CoopCtx {
     int id;
 };
 
-__device__ __forceinline__ void coop_tile(CoopCtx &c, const float4 *S_, int n, int base)
+template <int MODE>
+__device__ __forceinline__ void coop_tile(CoopCtx &c, const float4 *S_, const float4 *__restrict__ geo, float obound, int n,
+                                          int base)
 {
     if (!c.member)
         return;
-    for (int j = c.r; j < n; j += c.S) {
-        if (tri_quick(c.o, c.d, S_[3 * j], S_[3 * j + 1], S_[3 * j + 2])) {
-            unsigned dummy[1];
-            tri_test_exact<false>(c.o, c.d, S_[3 * j], S_[3 * j + 1], S_[3 * j + 2], base + j, c.best, c.id, dummy);
-        }
+    unsigned dummy[1];
+    if (MODE == 0) {
+        for (int j = c.r; j < n; j += c.S)
+            if (tri_quick(c.o, c.d, S_[3 * j], S_[3 * j + 1], S_[3 * j + 2]))
+                tri_test_exact<false>(c.o, c.d, S_[3 * j], S_[3 * j + 1], S_[3 * j + 2], base + j, c.best, c.id, dummy);
+    } else {
+        const bool rayok = quick_ray_ok(c.o, c.d, obound);
+        for (int j = c.r; j < n; j += c.S)
+            if (!rayok || tri_quick2(c.o, c.d, S_[4 * j], S_[4 * j + 1], S_[4 * j + 2], S_[4 * j + 3])) {
+                const int i = base + j;
+                tri_test_exact<false>(c.o, c.d, __ldg(&geo[3 * i]), __ldg(&geo[3 * i + 1]), __ldg(&geo[3 * i + 2]), i, c.best, c.id,
+                                      dummy);
+            }
     }
 }
 
-template <bool STREAM>
+template <bool STREAM, int MODE>
 __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const RenderArgs a, const PathWork w)
 {
     extern __shared__ float4 sGeo[];
+    constexpr int RS = path_rec_f4(MODE);                 // float4 per triangle in shared memory
+    const float4 *const src = MODE == 0 ? a.sc.geo : w.qrec; // what phase 1 reads
     __shared__ uint64_t bars[2];
     const int ntris = a.sc.ntris;
     const int nsph = a.trianglesOnly ? 0 : a.sc.nsph;
@@ -171,8 +350,8 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
     const int ntiles = STREAM ? (ntris + tile - 1) / tile : 1;
 
     if (!STREAM) {
-        for (int i = threadIdx.x; i < 3 * ntris; i += PATH_THREADS)
-            sGeo[i] = a.sc.geo[i];
+        for (int i = threadIdx.x; i < RS * ntris; i += PATH_THREADS)
+            sGeo[i] = src[i];
     } else if (threadIdx.x == 0) {
         mbar_init(&bars[0], 1);
         mbar_init(&bars[1], 1);
@@ -203,14 +382,15 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
     int id0 = -1, bestId = -1;
     bool pend = false; // (best, bestId) of the last sweep is a hit that is not shaded yet
     unsigned long long nrays = 0, nhitpix = 0;
+    unsigned viol = 0; // MODE 2: accepted pairs the quick test dropped (must stay 0)
     uint32_t k0 = 0; // tiles consumed so far (STREAM): stage = k & 1, parity = (k >> 1) & 1
 
     auto issue = [&](uint32_t k, int t) {
         const int n = min(tile, ntris - t * tile);
-        const uint32_t bytes = (uint32_t)n * 3u * (uint32_t)sizeof(float4);
+        const uint32_t bytes = (uint32_t)n * (uint32_t)RS * (uint32_t)sizeof(float4);
         fence_proxy_async();
         mbar_arrive_expect_tx(&bars[k & 1], bytes);
-        tma_load_1d(sGeo + (size_t)(k & 1) * PATH_TILE * 3, a.sc.geo + (size_t)t * tile * 3, bytes, &bars[k & 1]);
+        tma_load_1d(sGeo + (size_t)(k & 1) * PATH_TILE * RS, src + (size_t)t * tile * RS, bytes, &bars[k & 1]);
     };
 
     // a path has ended: accumulate it (main.c:99) and start the next sample, or finish the pixel
@@ -367,10 +547,10 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
         }
         if (!STREAM) {
             if (coop || grouped) {
-                coop_tile(cc, sGeo, ntris, 0);
+                coop_tile<MODE>(cc, sGeo, a.sc.geo, w.obound, ntris, 0);
                 coop_finish();
             } else {
-                sweep_chunked(sGeo, ntris, 0, active, L.pos, L.dir, best, bestId);
+                sweep_chunked<MODE>(sGeo, a.sc.geo, w.obound, ntris, 0, active, L.pos, L.dir, best, bestId, viol);
             }
         } else {
             if (threadIdx.x == 0) {
@@ -382,10 +562,11 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
                 const uint32_t k = k0 + (uint32_t)t;
                 mbar_wait(&bars[k & 1], (k >> 1) & 1u);
                 if (coop || grouped)
-                    coop_tile(cc, sGeo + (size_t)(k & 1) * PATH_TILE * 3, min(tile, ntris - t * tile), t * tile);
+                    coop_tile<MODE>(cc, sGeo + (size_t)(k & 1) * PATH_TILE * RS, a.sc.geo, w.obound,
+                                    min(tile, ntris - t * tile), t * tile);
                 else
-                    sweep_chunked(sGeo + (size_t)(k & 1) * PATH_TILE * 3, min(tile, ntris - t * tile), t * tile,
-                                  active, L.pos, L.dir, best, bestId);
+                    sweep_chunked<MODE>(sGeo + (size_t)(k & 1) * PATH_TILE * RS, a.sc.geo, w.obound,
+                                        min(tile, ntris - t * tile), t * tile, active, L.pos, L.dir, best, bestId, viol);
                 __syncthreads(); // every warp is done with this stage
                 if (threadIdx.x == 0 && t + 2 < ntiles)
                     issue(k + 2, t + 2);
@@ -423,6 +604,8 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
             r += __shfl_xor_sync(0xffffffffu, r, o);
             hp += __shfl_xor_sync(0xffffffffu, hp, o);
         }
+        if (MODE == 2 && viol)
+            atomicAdd(&a.stats[ST_MISMATCH], (unsigned long long)viol);
         if (lane == 0 && r) {
             atomicAdd(&a.stats[ST_RAYS], r);
             atomicAdd(&a.stats[ST_TRI_PAIRS], r * (unsigned long long)ntris);
