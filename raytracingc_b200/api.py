@@ -15,7 +15,8 @@ from dataclasses import dataclass, field
 import numpy as np
 
 PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG, "librtc_b200.so")
+# RTC_B200_LIB: an alternative build of the same library (A/B measurements of compile-time variants)
+LIB_PATH = os.environ.get("RTC_B200_LIB") or os.path.join(PKG, "librtc_b200.so")
 
 # reference raytracing.h:41-45 (Triangle, 68 B) and :34-39 (Sphere, 36 B)
 TRI_DTYPE = np.dtype(

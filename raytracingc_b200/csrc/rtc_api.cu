@@ -375,6 +375,7 @@ rtc::RenderArgs make_args(const RtcScene *sc, const Scene *sky, const Camera *ca
     a.sky.ground = to3(sky->groundColor);
     a.sky.sunFocus = sky->sunFocus;
     a.sky.sunIntensity = sky->sunIntensity;
+    a.sky.sun_skip_ok = (sky->sunFocus >= 0.0f && std::isfinite(sky->sunIntensity)) ? 1 : 0;
     a.origin = to3(cam->origin);
     a.ex = to3(cam->ex);
     a.ey = to3(cam->ey);

@@ -138,7 +138,7 @@ __device__ __forceinline__ void shade_miss(Lane &L, const RenderArgs &a)
 }
 
 // hit (bestId != -1): raytracing.c:272-287; returns true when the path is finished
-__device__ __noinline__ bool shade_hit(Lane &L, const RenderArgs &a, float best, int bestId)
+__device__ __forceinline__ bool shade_hit(Lane &L, const RenderArgs &a, float best, int bestId)
 {
     // closest.hitPoint = pos + dir*dst (raytracing.c:238)
     f3 hp = xadd3(L.pos, xscale3(L.dir, best));
@@ -157,7 +157,9 @@ __device__ __noinline__ bool shade_hit(Lane &L, const RenderArgs &a, float best,
         smooth = __ldg(&a.sc.s2[k]);
     }
     f3 color = mk3(m0.x, m0.y, m0.z);
-    f3 diffuse = xnormalize(xadd3(n, random_direction(L.rng))); // :274
+    const float4 rd = random_direction(L.rng);
+    L.rng = __float_as_uint(rd.w);
+    f3 diffuse = xnormalize(xadd3(n, mk3(rd.x, rd.y, rd.z))); // :274
     f3 specular = xreflect(L.dir, n);                           // :275
     L.dir = xlerp(diffuse, specular, smooth);                   // :276, not renormalised
     L.pos = hp;                                                 // :277

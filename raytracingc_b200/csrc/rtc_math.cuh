@@ -99,7 +99,7 @@ __device__ __forceinline__ float random_value(uint32_t &state) { return rng_to_u
 
 // RandomValueNormalDistrubtion (moremath.c:98-103): all in double, narrowed
 // three times exactly where the reference's `float` locals narrow.
-__device__ __noinline__ float random_normal(uint32_t &state)
+__device__ __forceinline__ float random_normal(uint32_t &state)
 {
     float u1 = random_value(state); // theta's draw comes first
     float u2 = random_value(state);
@@ -107,35 +107,51 @@ __device__ __noinline__ float random_normal(uint32_t &state)
     float rho = (float)__dsqrt_rn(__dmul_rn(-2.0, log((double)u2)));
     return (float)__dmul_rn((double)rho, cos((double)theta));
 }
-// RandomDiretion (moremath.c:105-109): x, then y, then z, then normalized
-__device__ __forceinline__ f3 random_direction(uint32_t &state)
+// RandomDiretion (moremath.c:105-109): x, then y, then z, then normalized.
+// The call unit of the FP64 island: state in, {direction, state bits} out, all in registers; the three
+// deviates are inlined side by side so their log / cos / sqrt chains overlap.
+__device__ __noinline__ float4 random_direction(uint32_t state)
 {
     float x = random_normal(state);
     float y = random_normal(state);
     float z = random_normal(state);
-    return xnormalize(mk3(x, y, z));
+    f3 v = xnormalize(mk3(x, y, z));
+    return make_float4(v.x, v.y, v.z, __uint_as_float(state));
 }
 
 // ---- sky, reference raytracing.c:151-160 ------------------------------------
 struct SkyParams {
     f3 sun, horizon, zenith, ground;
     float sunFocus, sunIntensity;
+    int sun_skip_ok; // host: sunFocus >= 0 and sunIntensity finite (see environment_light)
 };
 
 // glibc's powf is < 1 ulp; CUDA's powf is several ulp, so evaluate in double
 // and narrow.
 __device__ __noinline__ float xpowf(float x, float y) { return (float)pow((double)x, (double)y); }
 
-__device__ __noinline__ f3 environment_light(f3 dir, const SkyParams &s)
+// Two exact shortcuts around the powf calls (the most expensive instructions of a miss):
+//  * powf(+0, .35) = +0 and powf(1, .35) = 1 exactly (smoothstep clamps, so below the horizon line and above
+//    -dir.y = .74 the argument IS 0 or 1);
+//  * when sunMask = 0 the sun term is sun * 0: for d <= 1, sunFocus >= 0 and a finite intensity the power is a
+//    finite number in [0, 1] whatever its value, so the product is a zero with the intensity's sign;
+//    powf(+0, focus > 0) = +0 likewise.
+__device__ __forceinline__ f3 environment_light(f3 dir, const SkyParams &s)
 {
-    float t = xpowf(xsmoothstep(0.0f, 0.74f, -dir.y), 0.35f);
+    const float x = xsmoothstep(0.0f, 0.74f, -dir.y);
+    const float t = x == 0.0f ? 0.0f : (x == 1.0f ? 1.0f : xpowf(x, 0.35f));
     f3 grad = xlerp(s.horizon, s.zenith, t);
     float d = xdot(dir, s.sun);
     d = (d > 0.0f) ? d : 0.0f; // fmax(0, d): NaN -> 0
-    float sun = xmul(xpowf(d, s.sunFocus), s.sunIntensity);
+    const bool masked = !(dir.y < 0.0f);
+    float sv;
+    if (masked && d <= 1.0f && s.sun_skip_ok) {
+        sv = copysignf(0.0f, s.sunIntensity);
+    } else {
+        const float pw = (d == 0.0f && s.sunFocus > 0.0f) ? 0.0f : xpowf(d, s.sunFocus);
+        sv = xmul(xmul(pw, s.sunIntensity), masked ? 0.0f : 1.0f);
+    }
     float g2s = xsmoothstep(-0.01f, 0.0f, -dir.y);
-    float mask = dir.y < 0.0f ? 1.0f : 0.0f;
-    float sv = xmul(sun, mask);
     f3 base = xlerp(s.ground, grad, g2s);
     return mk3(xadd(base.x, sv), xadd(base.y, sv), xadd(base.z, sv));
 }

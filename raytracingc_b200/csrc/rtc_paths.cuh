@@ -22,6 +22,14 @@
 namespace rtc {
 
 constexpr int PATH_THREADS = 128;
+#ifndef RTC_QUICK_UNROLL
+#define RTC_QUICK_UNROLL 4 // pairs per iteration of the branch-free first phase; A/B knob
+#endif
+#ifdef RTC_PATH_MINBLOCKS // min resident CTAs per SM asked of the compiler (register cap); A/B knob
+#define RTC_PATH_BOUNDS __launch_bounds__(PATH_THREADS, RTC_PATH_MINBLOCKS)
+#else
+#define RTC_PATH_BOUNDS __launch_bounds__(PATH_THREADS)
+#endif
 constexpr int PATH_TILE = 256; // triangles per streamed tile: 12 KB per stage, 2 stages (occupancy stays register-bound)
 
 struct PathWork {
@@ -215,6 +223,16 @@ __device__ __forceinline__ void tri_quick2_bit(const f3 &o, const f3 &d, const f
         : "f"(v.U), "f"(nmu), "f"(v.V), "f"(v.sum), "f"(v.hi), "f"(v.det), "f"(v.mu), "f"(v.thr), "n"(BIT));
 }
 
+// K-th .. (N-1)-th pair of a group of N consecutive records: bit K of mg
+template <int K, int N>
+__device__ __forceinline__ void quick2_group(const f3 &o, const f3 &d, const float4 *R, unsigned &mg)
+{
+    if constexpr (K < N) {
+        tri_quick2_bit<(1u << K)>(o, d, R[4 * K], R[4 * K + 1], R[4 * K + 2], R[4 * K + 3], mg);
+        quick2_group<K + 1, N>(o, d, R, mg);
+    }
+}
+
 // a ray the quick records are valid for (see above); other rays send every pair to phase 2
 __device__ __forceinline__ bool quick_ray_ok(const f3 &o, const f3 &d, float obound)
 {
@@ -255,20 +273,16 @@ __device__ __forceinline__ void sweep_chunked(const float4 *S, const float4 *__r
                     m |= m1 << j;
                 }
             } else {
+                constexpr int UN = RTC_QUICK_UNROLL;
                 int j = 0;
-                for (; j + 4 <= cn; j += 4) {
-                    const float4 *R = S + 4 * (c0 + j);
-                    unsigned m4 = 0;
-                    tri_quick2_bit<1u>(o, d, R[0], R[1], R[2], R[3], m4);
-                    tri_quick2_bit<2u>(o, d, R[4], R[5], R[6], R[7], m4);
-                    tri_quick2_bit<4u>(o, d, R[8], R[9], R[10], R[11], m4);
-                    tri_quick2_bit<8u>(o, d, R[12], R[13], R[14], R[15], m4);
-                    m |= m4 << j;
+                for (; j + UN <= cn; j += UN) {
+                    unsigned mg = 0;
+                    quick2_group<0, UN>(o, d, S + 4 * (c0 + j), mg);
+                    m |= mg << j;
                 }
                 for (; j < cn; ++j) {
-                    const float4 *R = S + 4 * (c0 + j);
                     unsigned m1 = 0;
-                    tri_quick2_bit<1u>(o, d, R[0], R[1], R[2], R[3], m1);
+                    quick2_group<0, 1>(o, d, S + 4 * (c0 + j), m1);
                     m |= m1 << j;
                 }
             }
@@ -337,7 +351,7 @@ __device__ __forceinline__ void coop_tile(CoopCtx &c, const float4 *S_, const fl
 }
 
 template <bool STREAM, int MODE>
-__global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const RenderArgs a, const PathWork w)
+__global__ void RTC_PATH_BOUNDS render_paths_kernel(const RenderArgs a, const PathWork w)
 {
     extern __shared__ float4 sGeo[];
     constexpr int RS = path_rec_f4(MODE);                 // float4 per triangle in shared memory
@@ -422,9 +436,7 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
     };
 
     while (true) {
-        // ---- idle lanes fetch the next (pixel, plane) task; repeated while a lane finishes its pixel in the
-        //      shading pass below, so a warp never leaves (or sweeps with idle lanes) while work is left ----
-        do {
+        // ---- idle lanes fetch the next (pixel, plane) task ----
         {
             const bool need = !active && !exhausted; // identical on the S lanes of a group
             const unsigned m = __ballot_sync(0xffffffffu, need && gr == 0);
@@ -474,10 +486,12 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
                 }
             }
         }
-        // ---- hit shading, one pass for both kinds of pending hits: the hit the last sweep found, and the known
-        //      primary hit of a lane that starts a sample (the primary kernel sweeps that ray every sample).  A lane
-        //      whose path ends here starts its next sample in the same loop. ----
-        while (active && (pend || (has_rec && fresh))) {
+        // ---- hit shading, ONE pass per round for both kinds of pending hits: the hit the last sweep found, and the
+        //      known primary hit of a lane that starts a sample (the primary kernel sweeps that ray every sample).
+        //      A lane whose path ends here (Russian roulette, bounce limit) and whose next sample again starts from
+        //      a known hit sits out this round's sweep: repeating the pass for those few lanes would cost a full
+        //      shading pass at a few percent lane utilisation each time. ----
+        if (active && (pend || (has_rec && fresh))) {
             if (!pend) {
                 best = best0;
                 bestId = id0;
@@ -487,7 +501,8 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
             if (shade_hit(L, a, best, bestId))
                 finish_sample();
         }
-        } while (__any_sync(0xffffffffu, !active && !exhausted));
+        // lanes with a ray to sweep this round
+        const bool sweeping = active && !(has_rec && fresh);
         const bool any = STREAM ? (__syncthreads_or(active) != 0) : __any_sync(0xffffffffu, active);
         if (!any)
             break;
@@ -495,11 +510,11 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
         // ---- closest hit of the lane's current ray: spheres first, then triangles in order ----
         best = 999999.0f;
         bestId = -1;
-        if (active)
+        if (sweeping)
             for (int k = 0; k < nsph; ++k)
                 sphere_test_exact(L.pos, L.dir, __ldg(&a.sc.s0[k]), k, best, bestId);
         // few live lanes and nothing left to fetch: sweep cooperatively (see CoopCtx)
-        const unsigned act = __ballot_sync(0xffffffffu, active);
+        const unsigned act = __ballot_sync(0xffffffffu, sweeping);
         const int na = __popc(act);
         const bool coop = S == 1 && na > 0 && na <= 16 && w.coop;
         CoopCtx cc;
@@ -529,7 +544,7 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
             }
             const float gb = __shfl_sync(0xffffffffu, cc.best, cc.leader & 31);
             const int gi = __shfl_sync(0xffffffffu, cc.id, cc.leader & 31);
-            if (active && gi != -1 && gb < best) { // spheres were tested first by the owner: they win ties
+            if (sweeping && gi != -1 && gb < best) { // spheres were tested first by the owner: they win ties
                 best = gb;
                 bestId = gi;
             }
@@ -538,7 +553,7 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
         if (grouped) { // the group's lanes hold the same ray; member gr sweeps every S-th triangle
             cc.S = S;
             cc.r = gr;
-            cc.member = active;
+            cc.member = sweeping;
             cc.o = L.pos;
             cc.d = L.dir;
             cc.best = 999999.0f;
@@ -550,7 +565,7 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
                 coop_tile<MODE>(cc, sGeo, a.sc.geo, w.obound, ntris, 0);
                 coop_finish();
             } else {
-                sweep_chunked<MODE>(sGeo, a.sc.geo, w.obound, ntris, 0, active, L.pos, L.dir, best, bestId, viol);
+                sweep_chunked<MODE>(sGeo, a.sc.geo, w.obound, ntris, 0, sweeping, L.pos, L.dir, best, bestId, viol);
             }
         } else {
             if (threadIdx.x == 0) {
@@ -566,7 +581,7 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
                                     min(tile, ntris - t * tile), t * tile);
                 else
                     sweep_chunked<MODE>(sGeo + (size_t)(k & 1) * PATH_TILE * RS, a.sc.geo, w.obound,
-                                        min(tile, ntris - t * tile), t * tile, active, L.pos, L.dir, best, bestId, viol);
+                                        min(tile, ntris - t * tile), t * tile, sweeping, L.pos, L.dir, best, bestId, viol);
                 __syncthreads(); // every warp is done with this stage
                 if (threadIdx.x == 0 && t + 2 < ntiles)
                     issue(k + 2, t + 2);
@@ -577,7 +592,7 @@ __global__ void __launch_bounds__(PATH_THREADS) render_paths_kernel(const Render
         }
 
         // ---- shade (calcColor's loop body), advance the state machine ----
-        if (active) {
+        if (sweeping) {
             nrays += gr == 0;
             if (first) {
                 first = false;
