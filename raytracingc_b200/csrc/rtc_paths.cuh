@@ -118,25 +118,28 @@ __device__ __forceinline__ void tri_quick_bit(const f3 &o, const f3 &d, const fl
 // ---- MODE 1: conservative quick test from per-triangle quick records ----------------------------------------
 //
 // Phase 1 does not have to use the reference's arithmetic -- it only has to keep every pair the reference
-// accepts; phase 2 (tri_test_exact, in index order) produces the result.  With w = s x d (s = o - A):
-//     s.(d x AC) = AC.w        d.(s x AB) = -AB.w        AB.(d x AC) = d.(AC x AB)
-// so the numerators of u and v and the determinant cost 20 FMA-pipe operations per pair (the reference's u alone
-// costs 29), and the test sees the whole triangle, not only the u strip.  The values differ from the reference's
-// floats by rounding only; mu (per triangle, built in double by quick_records_kernel) bounds
-// |reference's float - exact| + |this code's float - exact| for every ray with max|d_i| <= QUICK_DBOUND and
-// max|o_i| <= obound (other rays skip phase 1: all pairs go to phase 2):
-//     |sh_r - U|, |vn_r - V| <= 2^-17 (obound + max|A_i|) Dmax Emax        (73 u S Dmax Emax, u = 2^-24)
+// accepts; phase 2 (tri_test_exact, in index order) produces the result.  With s = o - A and the ray's moment
+// m = o x d (computed once per sweep):
+//     s.(d x AC) =  AC.m + (A x AC).d        d.(s x AB) = -AB.m - (A x AB).d        AB.(d x AC) = (AC x AB).d
+// so the numerators of u and v and the determinant are three dot products against per-triangle constants: 18
+// FMA-pipe operations per pair (the reference's u alone costs 29), and the test sees the whole triangle, not only
+// the u strip.  The values differ from the reference's floats by rounding only; M (per triangle, built in double
+// by quick_records_kernel) bounds 4 x ( |reference's float - exact| + |this code's float - exact| ) for every
+// ray with max|d_i| <= QUICK_DBOUND and max|o_i| <= obound (other rays skip phase 1: all pairs go to phase 2):
+//     |sh_r - U|, |vn_r - V| <= 2^-17 (obound + max|A_i|) Dmax Emax        (85 u (..), u = 2^-24)
 //     |det_r - det|          <= 2^-18 Dmax Emax^2                           (55 u), Emax = max |AB_i|, |AC_i|
-// The record holds the edges and N = AC x AB multiplied by f = +-1 so that "det~ > 0" means "front facing by the
-// stored normal" (n = lambda N + e, lambda and e computed in double; f = -sign(lambda)).  A pair is dropped when
-//   det~ < thr      det~ <= -X: c_r = fl(d.n) >= 0 (cull, raytracing.c:189), X = mu + Dmax (2^-19 nmax + 3 emax)/|lambda|;
-//                   |det~| < EPS - mu: |det_r| < EPS (raytracing.c:195).  thr = EPS - mu if X + mu < EPS, else -X
-//   det~ > mu (the sign of det_r is known) and one of
-//     U~ < -mu          u_r < 0  (mu >= 1e-18 keeps fl(sh_r * inv_r) away from -0)
-//     V~ < -mu          v_r < 0
-//     U~ + V~ > det~ (1 + 2^-19) + 4 mu      then u_r > 1, or fl(u_r + v_r) > 1 (u_r, v_r >= 0 carry <= 2.01 u each)
-// Every comparison keeps the pair when unordered (NaN) and degenerate triangles get mu = inf, thr = -inf.
+// The record holds its vectors multiplied by f = +-1 so that "det~ > 0" means "front facing by the stored
+// normal" (n = lambda N + e with N = AC x AB, lambda and e computed in double; f = -sign(lambda)).
+// A pair is dropped when
+//   det~ < thr      det~ <= -X: c_r = fl(d.n) >= 0 (cull, raytracing.c:189), X = M + Dmax (2^-19 nmax + 3 emax)/|lambda|;
+//                   |det~| < EPS - M: |det_r| < EPS (raytracing.c:195).  thr = EPS - M if X + M < EPS, else -X
+//   det~ > M' (the sign of det_r is known), M' = EPS - thr >= M, and one of
+//     U~ < -M'          u_r < 0  (M >= 1e-18 keeps fl(sh_r * inv_r) away from -0)
+//     V~ < -M'          v_r < 0
+//     U~ + V~ > det~ (1 + 2^-19) + M'      then u_r > 1, or fl(u_r + v_r) > 1 (u_r, v_r >= 0 carry <= 2.01 u each)
+// Every comparison keeps the pair when unordered (NaN) and degenerate triangles get thr = -inf (M' = inf).
 constexpr float QUICK_DBOUND = 1.0625f;
+constexpr float QUICK_EPS = 0.0009999f; // just below the reference's 0.001f
 
 __global__ void quick_records_kernel(const float4 *__restrict__ geo, int n, float obound, float4 *__restrict__ q)
 {
@@ -144,92 +147,109 @@ __global__ void quick_records_kernel(const float4 *__restrict__ geo, int n, floa
     if (i >= n)
         return;
     const float4 g0 = geo[3 * i], g1 = geo[3 * i + 1], g2 = geo[3 * i + 2];
-    const double ab[3] = {g1.x, g1.y, g1.z}, ac[3] = {g2.x, g2.y, g2.z}, nr[3] = {g0.w, g1.w, g2.w};
-    const double N[3] = {ac[1] * ab[2] - ac[2] * ab[1], ac[2] * ab[0] - ac[0] * ab[2], ac[0] * ab[1] - ac[1] * ab[0]};
+    const double A[3] = {g0.x, g0.y, g0.z}, ab[3] = {g1.x, g1.y, g1.z}, ac[3] = {g2.x, g2.y, g2.z}, nr[3] = {g0.w, g1.w, g2.w};
+    auto cross = [](const double *a, const double *b, double *c) {
+        c[0] = a[1] * b[2] - a[2] * b[1];
+        c[1] = a[2] * b[0] - a[0] * b[2];
+        c[2] = a[0] * b[1] - a[1] * b[0];
+    };
+    double N[3], PU[3], PV[3];
+    cross(ac, ab, N);  // AC x AB
+    cross(A, ac, PU);  // A x AC
+    cross(A, ab, PV);  // A x AB
     const double nn = nr[0] * N[0] + nr[1] * N[1] + nr[2] * N[2];
     const double NN = N[0] * N[0] + N[1] * N[1] + N[2] * N[2];
     const double Em = fmax(fmax(fmax(fabs(ab[0]), fabs(ab[1])), fabs(ab[2])), fmax(fmax(fabs(ac[0]), fabs(ac[1])), fabs(ac[2])));
-    const double At = fmax(fmax(fabs((double)g0.x), fabs((double)g0.y)), fabs((double)g0.z));
+    const double At = fmax(fmax(fabs(A[0]), fabs(A[1])), fabs(A[2]));
     const double nm = fmax(fmax(fabs(nr[0]), fabs(nr[1])), fabs(nr[2]));
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
     const double Db = (double)QUICK_DBOUND;
-    double mu = inf, thr = -inf, f = 1.0;
-    // written so that NaN or inf anywhere leaves mu = inf, thr = -inf (the pair always goes to phase 2)
+    double thr = -inf, f = 1.0;
+    // written so that NaN or inf anywhere leaves thr = -inf (the pair always goes to phase 2)
     if (NN > 0.0 && NN < 1e40 && Em < 1e10 && At < 1e10 && nm < 1e10 && (double)obound < 1e10) {
         const double lam = nn / NN;
         const double e0 = nr[0] - lam * N[0], e1 = nr[1] - lam * N[1], e2 = nr[2] - lam * N[2];
         const double em = fmax(fmax(fabs(e0), fabs(e1)), fabs(e2)) * (1.0 + 1e-9) + 1e-12 * nm;
         f = lam < 0.0 ? 1.0 : -1.0;
-        const double m = fmax(0x1p-17 * ((double)obound + At) * Db * Em, 0x1p-18 * Db * Em * Em) * 1.01 + 1e-18;
+        const double mu = fmax(0x1p-17 * ((double)obound + At) * Db * Em, 0x1p-18 * Db * Em * Em) * 1.01 + 1e-18;
+        const double M = 4.0 * mu;
         const double alam = fabs(lam);
-        const double X = alam > 0.0 ? m + Db * (0x1p-19 * nm + 3.0 * em + 1e-30) / alam * 1.01 : inf;
-        const double EPSq = 0.0009999;
-        mu = m;
-        thr = (X + m < EPSq) ? EPSq - m : -X;
+        const double X = alam > 0.0 ? M + Db * (0x1p-19 * nm + 3.0 * em + 1e-30) / alam * 1.01 : inf;
+        thr = (X + M < (double)QUICK_EPS) ? (double)QUICK_EPS - M : -X;
     }
     const float fs = (float)f;
-    q[4 * i + 0] = make_float4(g0.x, g0.y, g0.z, __double2float_ru(mu));
-    q[4 * i + 1] = make_float4(-fs * g1.x, -fs * g1.y, -fs * g1.z, __double2float_rd(thr));
-    q[4 * i + 2] = make_float4(fs * g2.x, fs * g2.y, fs * g2.z, __double2float_ru(4.0 * mu));
-    q[4 * i + 3] = make_float4(fs * (float)N[0], fs * (float)N[1], fs * (float)N[2], 0.0f);
+    q[4 * i + 0] = make_float4(fs * g2.x, fs * g2.y, fs * g2.z, fs * (float)PU[0]);                   // AC~, PU~.x
+    q[4 * i + 1] = make_float4(fs * (float)PU[1], fs * (float)PU[2], -fs * g1.x, -fs * g1.y);         // PU~.yz, -AB~.xy
+    q[4 * i + 2] = make_float4(-fs * g1.z, -fs * (float)PV[0], -fs * (float)PV[1], -fs * (float)PV[2]); // -AB~.z, -PV~
+    q[4 * i + 3] = make_float4(fs * (float)N[0], fs * (float)N[1], fs * (float)N[2], __double2float_rd(thr));
+}
+
+// the ray's side of the quick test: direction and moment
+struct QuickRay {
+    f3 d, m;
+};
+__device__ __forceinline__ QuickRay quick_ray(const f3 &o, const f3 &d)
+{
+    QuickRay r;
+    r.d = d;
+    r.m = mk3(fmaf(o.y, d.z, -(o.z * d.y)), fmaf(o.z, d.x, -(o.x * d.z)), fmaf(o.x, d.y, -(o.y * d.x)));
+    return r;
 }
 
 // the values of the quick test for one pair (see above); FMUL + FFMA chains, no attempt to match the reference's rounding
 struct QuickVals {
-    float U, V, det, sum, hi, mu, thr;
+    float U, V, det, sum, hi, M, thr;
 };
-__device__ __forceinline__ QuickVals quick_vals(const f3 &o, const f3 &d, const float4 &r0, const float4 &r1, const float4 &r2,
+__device__ __forceinline__ QuickVals quick_vals(const QuickRay &r, const float4 &r0, const float4 &r1, const float4 &r2,
                                                 const float4 &r3)
 {
     QuickVals v;
-    const float sx = o.x - r0.x, sy = o.y - r0.y, sz = o.z - r0.z;
-    const float wx = fmaf(sy, d.z, -(sz * d.y)), wy = fmaf(sz, d.x, -(sx * d.z)), wz = fmaf(sx, d.y, -(sy * d.x));
-    v.U = fmaf(r2.z, wz, fmaf(r2.y, wy, r2.x * wx));
-    v.V = fmaf(r1.z, wz, fmaf(r1.y, wy, r1.x * wx));
-    v.det = fmaf(r3.z, d.z, fmaf(r3.y, d.y, r3.x * d.x));
+    v.U = fmaf(r1.y, r.d.z, fmaf(r1.x, r.d.y, fmaf(r0.w, r.d.x, fmaf(r0.z, r.m.z, fmaf(r0.y, r.m.y, r0.x * r.m.x)))));
+    v.V = fmaf(r2.w, r.d.z, fmaf(r2.z, r.d.y, fmaf(r2.y, r.d.x, fmaf(r2.x, r.m.z, fmaf(r1.w, r.m.y, r1.z * r.m.x)))));
+    v.det = fmaf(r3.z, r.d.z, fmaf(r3.y, r.d.y, r3.x * r.d.x));
     v.sum = v.U + v.V;
-    v.hi = fmaf(v.det, 1.0000019073486328f, r2.w);
-    v.mu = r0.w;
-    v.thr = r1.w;
+    v.thr = r3.w;
+    v.M = QUICK_EPS - v.thr;
+    v.hi = fmaf(v.det, 1.0000019073486328f, v.M);
     return v;
 }
 
-__device__ __forceinline__ bool tri_quick2(const f3 &o, const f3 &d, const float4 &r0, const float4 &r1, const float4 &r2,
+__device__ __forceinline__ bool tri_quick2(const QuickRay &r, const float4 &r0, const float4 &r1, const float4 &r2,
                                            const float4 &r3)
 {
-    const QuickVals v = quick_vals(o, d, r0, r1, r2, r3);
-    bool p = !(v.U < -v.mu);
-    p = p && !(v.V < -v.mu);
+    const QuickVals v = quick_vals(r, r0, r1, r2, r3);
+    bool p = !(v.U < -v.M);
+    p = p && !(v.V < -v.M);
     p = p && !(v.sum > v.hi);
-    p = p || !(v.det > v.mu);
+    p = p || !(v.det > v.M);
     p = p && !(v.det < v.thr);
     return p;
 }
 
 template <unsigned BIT>
-__device__ __forceinline__ void tri_quick2_bit(const f3 &o, const f3 &d, const float4 &r0, const float4 &r1, const float4 &r2,
+__device__ __forceinline__ void tri_quick2_bit(const QuickRay &r, const float4 &r0, const float4 &r1, const float4 &r2,
                                                const float4 &r3, unsigned &m)
 {
-    const QuickVals v = quick_vals(o, d, r0, r1, r2, r3);
-    const float nmu = -v.mu;
+    const QuickVals v = quick_vals(r, r0, r1, r2, r3);
+    const float nM = -v.M;
     asm("{\n\t.reg .pred p;\n\t"
-        "setp.geu.f32 p, %1, %2;\n\t"        // !(U < -mu)
-        "setp.geu.and.f32 p, %3, %2, p;\n\t" // !(V < -mu)
+        "setp.geu.f32 p, %1, %2;\n\t"        // !(U < -M)
+        "setp.geu.and.f32 p, %3, %2, p;\n\t" // !(V < -M)
         "setp.leu.and.f32 p, %4, %5, p;\n\t" // !(U + V > hi)
-        "setp.leu.or.f32 p, %6, %7, p;\n\t"  // or the sign of det is not known: !(det > mu)
+        "setp.leu.or.f32 p, %6, %7, p;\n\t"  // or the sign of det is not known: !(det > M)
         "setp.geu.and.f32 p, %6, %8, p;\n\t" // !(det < thr)
         "@p or.b32 %0, %0, %9;\n\t}"
         : "+r"(m)
-        : "f"(v.U), "f"(nmu), "f"(v.V), "f"(v.sum), "f"(v.hi), "f"(v.det), "f"(v.mu), "f"(v.thr), "n"(BIT));
+        : "f"(v.U), "f"(nM), "f"(v.V), "f"(v.sum), "f"(v.hi), "f"(v.det), "f"(v.M), "f"(v.thr), "n"(BIT));
 }
 
 // K-th .. (N-1)-th pair of a group of N consecutive records: bit K of mg
 template <int K, int N>
-__device__ __forceinline__ void quick2_group(const f3 &o, const f3 &d, const float4 *R, unsigned &mg)
+__device__ __forceinline__ void quick2_group(const QuickRay &r, const float4 *R, unsigned &mg)
 {
     if constexpr (K < N) {
-        tri_quick2_bit<(1u << K)>(o, d, R[4 * K], R[4 * K + 1], R[4 * K + 2], R[4 * K + 3], mg);
-        quick2_group<K + 1, N>(o, d, R, mg);
+        tri_quick2_bit<(1u << K)>(r, R[4 * K], R[4 * K + 1], R[4 * K + 2], R[4 * K + 3], mg);
+        quick2_group<K + 1, N>(r, R, mg);
     }
 }
 
@@ -250,6 +270,7 @@ __device__ __forceinline__ void sweep_chunked(const float4 *S, const float4 *__r
                                               unsigned &viol)
 {
     const bool rayok = MODE == 0 || quick_ray_ok(o, d, obound);
+    const QuickRay qr = quick_ray(o, d);
     for (int c0 = 0; c0 < n; c0 += 32) {
         const int cn = min(32, n - c0);
         unsigned m = 0;
@@ -277,12 +298,12 @@ __device__ __forceinline__ void sweep_chunked(const float4 *S, const float4 *__r
                 int j = 0;
                 for (; j + UN <= cn; j += UN) {
                     unsigned mg = 0;
-                    quick2_group<0, UN>(o, d, S + 4 * (c0 + j), mg);
+                    quick2_group<0, UN>(qr, S + 4 * (c0 + j), mg);
                     m |= mg << j;
                 }
                 for (; j < cn; ++j) {
                     unsigned m1 = 0;
-                    quick2_group<0, 1>(o, d, S + 4 * (c0 + j), m1);
+                    quick2_group<0, 1>(qr, S + 4 * (c0 + j), m1);
                     m |= m1 << j;
                 }
             }
@@ -341,8 +362,9 @@ __device__ __forceinline__ void coop_tile(CoopCtx &c, const float4 *S_, const fl
                 tri_test_exact<false>(c.o, c.d, S_[3 * j], S_[3 * j + 1], S_[3 * j + 2], base + j, c.best, c.id, dummy);
     } else {
         const bool rayok = quick_ray_ok(c.o, c.d, obound);
+        const QuickRay qr = quick_ray(c.o, c.d);
         for (int j = c.r; j < n; j += c.S)
-            if (!rayok || tri_quick2(c.o, c.d, S_[4 * j], S_[4 * j + 1], S_[4 * j + 2], S_[4 * j + 3])) {
+            if (!rayok || tri_quick2(qr, S_[4 * j], S_[4 * j + 1], S_[4 * j + 2], S_[4 * j + 3])) {
                 const int i = base + j;
                 tri_test_exact<false>(c.o, c.d, __ldg(&geo[3 * i]), __ldg(&geo[3 * i + 1]), __ldg(&geo[3 * i + 2]), i, c.best, c.id,
                                       dummy);
