@@ -30,7 +30,7 @@ constexpr int PATH_THREADS = 128;
 #else
 #define RTC_PATH_BOUNDS __launch_bounds__(PATH_THREADS)
 #endif
-constexpr int PATH_TILE = 256; // triangles per streamed tile: 12 KB per stage, 2 stages (occupancy stays register-bound)
+constexpr int PATH_TILE = 128; // triangles per streamed tile: 14 KB per stage (quick records + geometry), 2 stages
 
 struct PathWork {
     const int *list;            // compact pixel indices (cj * out_w + ci) or nullptr = all pixels
@@ -47,8 +47,8 @@ struct PathWork {
                                 // kernel sweeps primary rays itself
 };
 
-// float4 per triangle in shared memory: geometry (MODE 0) or quick record (MODE 1, 2)
-__host__ __device__ constexpr int path_rec_f4(int mode) { return mode == 0 ? 3 : 4; }
+// float4 per triangle in shared memory: geometry (3, what phase 2 reads) + in MODE 1, 2 the quick record (4, phase 1)
+__host__ __device__ constexpr int path_rec_f4(int mode) { return mode == 0 ? 3 : 7; }
 
 __host__ __device__ inline size_t path_smem_bytes(int ntris, bool stream, int mode)
 {
@@ -261,11 +261,11 @@ __device__ __forceinline__ bool quick_ray_ok(const f3 &o, const f3 &d, float obo
     return dm <= QUICK_DBOUND && om <= obound; // false for NaN
 }
 
-// MODE 0: S = geometry tile (3 float4 per triangle), quick test in the reference's arithmetic.
-// MODE 1: S = quick-record tile (4 float4 per triangle); phase 2 reads the geometry through the read-only cache.
+// MODE 0: S = geo = geometry tile (3 float4 per triangle), quick test in the reference's arithmetic.
+// MODE 1: S = quick-record tile (4 float4 per triangle), geo = geometry tile of the same triangles (phase 2).
 // MODE 2: MODE 1 + every pair also runs the exact test; an accepted pair the quick test dropped is counted (viol).
 template <int MODE>
-__device__ __forceinline__ void sweep_chunked(const float4 *S, const float4 *__restrict__ geo, float obound, int n, int base,
+__device__ __forceinline__ void sweep_chunked(const float4 *S, const float4 *geo, float obound, int n, int base,
                                               bool active, const f3 &o, const f3 &d, float &best, int &bestId,
                                               unsigned &viol)
 {
@@ -310,11 +310,11 @@ __device__ __forceinline__ void sweep_chunked(const float4 *S, const float4 *__r
         }
         if (MODE == 2 && active) {
             for (int j = 0; j < cn; ++j) {
-                const int i = base + c0 + j;
+                const int i = c0 + j;
                 unsigned ex[6] = {0, 0, 0, 0, 0, 0};
                 float b_ = 999999.0f;
                 int id_ = -1;
-                tri_test_exact<true>(o, d, __ldg(&geo[3 * i]), __ldg(&geo[3 * i + 1]), __ldg(&geo[3 * i + 2]), i, b_, id_, ex);
+                tri_test_exact<true>(o, d, geo[3 * i], geo[3 * i + 1], geo[3 * i + 2], base + i, b_, id_, ex);
                 if (ex[5] && !((m >> j) & 1u))
                     viol++;
             }
@@ -327,9 +327,8 @@ __device__ __forceinline__ void sweep_chunked(const float4 *S, const float4 *__r
                 tri_test_exact<false>(o, d, S[3 * (c0 + j)], S[3 * (c0 + j) + 1], S[3 * (c0 + j) + 2], base + c0 + j, best,
                                       bestId, dummy);
             } else {
-                const int i = base + c0 + j;
-                tri_test_exact<false>(o, d, __ldg(&geo[3 * i]), __ldg(&geo[3 * i + 1]), __ldg(&geo[3 * i + 2]), i, best, bestId,
-                                      dummy);
+                const int i = c0 + j;
+                tri_test_exact<false>(o, d, geo[3 * i], geo[3 * i + 1], geo[3 * i + 2], base + i, best, bestId, dummy);
             }
         }
     }
@@ -350,8 +349,7 @@ struct CoopCtx {
 };
 
 template <int MODE>
-__device__ __forceinline__ void coop_tile(CoopCtx &c, const float4 *S_, const float4 *__restrict__ geo, float obound, int n,
-                                          int base)
+__device__ __forceinline__ void coop_tile(CoopCtx &c, const float4 *S_, const float4 *geo, float obound, int n, int base)
 {
     if (!c.member)
         return;
@@ -364,11 +362,8 @@ __device__ __forceinline__ void coop_tile(CoopCtx &c, const float4 *S_, const fl
         const bool rayok = quick_ray_ok(c.o, c.d, obound);
         const QuickRay qr = quick_ray(c.o, c.d);
         for (int j = c.r; j < n; j += c.S)
-            if (!rayok || tri_quick2(qr, S_[4 * j], S_[4 * j + 1], S_[4 * j + 2], S_[4 * j + 3])) {
-                const int i = base + j;
-                tri_test_exact<false>(c.o, c.d, __ldg(&geo[3 * i]), __ldg(&geo[3 * i + 1]), __ldg(&geo[3 * i + 2]), i, c.best, c.id,
-                                      dummy);
-            }
+            if (!rayok || tri_quick2(qr, S_[4 * j], S_[4 * j + 1], S_[4 * j + 2], S_[4 * j + 3]))
+                tri_test_exact<false>(c.o, c.d, geo[3 * j], geo[3 * j + 1], geo[3 * j + 2], base + j, c.best, c.id, dummy);
     }
 }
 
@@ -376,8 +371,9 @@ template <bool STREAM, int MODE>
 __global__ void RTC_PATH_BOUNDS render_paths_kernel(const RenderArgs a, const PathWork w)
 {
     extern __shared__ float4 sGeo[];
-    constexpr int RS = path_rec_f4(MODE);                 // float4 per triangle in shared memory
-    const float4 *const src = MODE == 0 ? a.sc.geo : w.qrec; // what phase 1 reads
+    // shared memory (per stage when streaming): [quick records, 4 float4 per triangle (MODE >= 1)][geometry, 3 per triangle]
+    constexpr int RS = path_rec_f4(MODE), QS = RS - 3;
+    const int cap = STREAM ? PATH_TILE : a.sc.ntris; // triangles a stage holds
     __shared__ uint64_t bars[2];
     const int ntris = a.sc.ntris;
     const int nsph = a.trianglesOnly ? 0 : a.sc.nsph;
@@ -386,8 +382,10 @@ __global__ void RTC_PATH_BOUNDS render_paths_kernel(const RenderArgs a, const Pa
     const int ntiles = STREAM ? (ntris + tile - 1) / tile : 1;
 
     if (!STREAM) {
-        for (int i = threadIdx.x; i < RS * ntris; i += PATH_THREADS)
-            sGeo[i] = src[i];
+        for (int i = threadIdx.x; i < QS * ntris; i += PATH_THREADS)
+            sGeo[i] = w.qrec[i];
+        for (int i = threadIdx.x; i < 3 * ntris; i += PATH_THREADS)
+            sGeo[QS * cap + i] = a.sc.geo[i];
     } else if (threadIdx.x == 0) {
         mbar_init(&bars[0], 1);
         mbar_init(&bars[1], 1);
@@ -423,10 +421,13 @@ __global__ void RTC_PATH_BOUNDS render_paths_kernel(const RenderArgs a, const Pa
 
     auto issue = [&](uint32_t k, int t) {
         const int n = min(tile, ntris - t * tile);
-        const uint32_t bytes = (uint32_t)n * (uint32_t)RS * (uint32_t)sizeof(float4);
+        const uint32_t bq = (uint32_t)n * (uint32_t)QS * (uint32_t)sizeof(float4), bg = (uint32_t)n * 3u * (uint32_t)sizeof(float4);
+        float4 *stage = sGeo + (size_t)(k & 1) * PATH_TILE * RS;
         fence_proxy_async();
-        mbar_arrive_expect_tx(&bars[k & 1], bytes);
-        tma_load_1d(sGeo + (size_t)(k & 1) * PATH_TILE * RS, src + (size_t)t * tile * RS, bytes, &bars[k & 1]);
+        mbar_arrive_expect_tx(&bars[k & 1], bq + bg);
+        if (QS)
+            tma_load_1d(stage, w.qrec + (size_t)t * tile * QS, bq, &bars[k & 1]);
+        tma_load_1d(stage + QS * PATH_TILE, a.sc.geo + (size_t)t * tile * 3, bg, &bars[k & 1]);
     };
 
     // a path has ended: accumulate it (main.c:99) and start the next sample, or finish the pixel
@@ -525,7 +526,10 @@ __global__ void RTC_PATH_BOUNDS render_paths_kernel(const RenderArgs a, const Pa
         }
         // lanes with a ray to sweep this round
         const bool sweeping = active && !(has_rec && fresh);
-        const bool any = STREAM ? (__syncthreads_or(active) != 0) : __any_sync(0xffffffffu, active);
+        // a lane that finished its pixel in the pass above fetches at the top of the next round: the warp leaves
+        // only when no lane has work AND the list is exhausted
+        const bool live = active || !exhausted;
+        const bool any = STREAM ? (__syncthreads_or(live) != 0) : __any_sync(0xffffffffu, live);
         if (!any)
             break;
 
@@ -584,10 +588,10 @@ __global__ void RTC_PATH_BOUNDS render_paths_kernel(const RenderArgs a, const Pa
         }
         if (!STREAM) {
             if (coop || grouped) {
-                coop_tile<MODE>(cc, sGeo, a.sc.geo, w.obound, ntris, 0);
+                coop_tile<MODE>(cc, sGeo, sGeo + QS * cap, w.obound, ntris, 0);
                 coop_finish();
             } else {
-                sweep_chunked<MODE>(sGeo, a.sc.geo, w.obound, ntris, 0, sweeping, L.pos, L.dir, best, bestId, viol);
+                sweep_chunked<MODE>(sGeo, sGeo + QS * cap, w.obound, ntris, 0, sweeping, L.pos, L.dir, best, bestId, viol);
             }
         } else {
             if (threadIdx.x == 0) {
@@ -598,12 +602,12 @@ __global__ void RTC_PATH_BOUNDS render_paths_kernel(const RenderArgs a, const Pa
             for (int t = 0; t < ntiles; ++t) {
                 const uint32_t k = k0 + (uint32_t)t;
                 mbar_wait(&bars[k & 1], (k >> 1) & 1u);
+                const float4 *stage = sGeo + (size_t)(k & 1) * PATH_TILE * RS;
                 if (coop || grouped)
-                    coop_tile<MODE>(cc, sGeo + (size_t)(k & 1) * PATH_TILE * RS, a.sc.geo, w.obound,
-                                    min(tile, ntris - t * tile), t * tile);
+                    coop_tile<MODE>(cc, stage, stage + QS * PATH_TILE, w.obound, min(tile, ntris - t * tile), t * tile);
                 else
-                    sweep_chunked<MODE>(sGeo + (size_t)(k & 1) * PATH_TILE * RS, a.sc.geo, w.obound,
-                                        min(tile, ntris - t * tile), t * tile, sweeping, L.pos, L.dir, best, bestId, viol);
+                    sweep_chunked<MODE>(stage, stage + QS * PATH_TILE, w.obound, min(tile, ntris - t * tile), t * tile,
+                                        sweeping, L.pos, L.dir, best, bestId, viol);
                 __syncthreads(); // every warp is done with this stage
                 if (threadIdx.x == 0 && t + 2 < ntiles)
                     issue(k + 2, t + 2);

@@ -46,3 +46,8 @@ s = stats.cpu().numpy()
 print(f"C5 lattice step {a.step}: {job.out_w}x{job.out_h} px of 3840x2160, {a.ntris} triangles, {a.spp} spp, nsplit "
       f"{a.nsplit}: {ms:.1f} ms, rays {int(s[0])}, pairs {int(s[1]):.3e}, {s[1] / ms / 1e6:.1f} G pairs/s, "
       f"{s[0] / ms / 1e3:.3f} Mrays/s, mismatches {int(s[11])}, mean image {rgb.float().mean().item():.2f}")
+if a.flags & api.RTC_FLAG_TIME_KERNELS:
+    pm, qm = sc.kernel_times()
+    nprim = job.out_w * job.out_h * a.spp
+    print(f"  primary kernels {pm:.1f} ms ({nprim * a.ntris / pm / 1e6:.1f} G pairs/s over {nprim} primary rays), "
+          f"path kernel {qm:.1f} ms ({(int(s[0]) - nprim) * a.ntris / qm / 1e6:.1f} G pairs/s over {int(s[0]) - nprim} bounce rays)")
