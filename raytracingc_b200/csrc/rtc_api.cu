@@ -98,6 +98,11 @@ struct RtcScene {
     float q_obound = 0.f;         // origin bound the records were built for; 0 = not built for the current scene
     float bound_abs = 0.f;        // max |coordinate| over triangle vertices and sphere extents (host scan at upload)
     bool quick_ok = false;        // the stored normals follow the winding closely enough for the quick records to pay
+    // pipelined device->host copy of render_cuda (one-shot, consumed by the next render): see RenderArgs::prog
+    unsigned *prog = nullptr;
+    int prog_rows = 0, prog_chunks = 0;
+    cudaEvent_t sky_ev = nullptr; // recorded when every pixel no later kernel rewrites is final (sky pixels)
+    bool sky_recorded = false;
 };
 
 extern "C" {
@@ -211,6 +216,8 @@ void rtc_scene_destroy(RtcScene *sc)
     for (auto &e : sc->kev)
         if (e)
             cudaEventDestroy(e);
+    if (sc->sky_ev)
+        cudaEventDestroy(sc->sky_ev);
     if (sc->fork_ev)
         cudaEventDestroy(sc->fork_ev);
     if (sc->join_ev)
@@ -605,8 +612,31 @@ int rtc_render_launch_count(const RtcScene *sc, const RtcDeviceJob *job, int wan
     return 4; // prepare_primary + block kernel + block-task kernel + path kernel (other modes launch 1-3)
 }
 
+static int render_device_impl(const RtcScene *sc, const Scene *sky, const Camera *cam, const RtcDeviceJob *job,
+                              uint8_t *d_rgb, float *d_accum, int32_t *d_ids, uint64_t *d_stats, void *stream);
+
 int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, const RtcDeviceJob *job,
                       uint8_t *d_rgb, float *d_accum, int32_t *d_ids, uint64_t *d_stats, void *stream)
+{
+    RtcScene *msc = const_cast<RtcScene *>(sc);
+    if (msc)
+        msc->sky_recorded = false;
+    int rc = render_device_impl(sc, sky, cam, job, d_rgb, d_accum, d_ids, d_stats, stream);
+    if (msc && msc->prog) {
+        // whatever path the frame took, every chunk is final once the stream gets here
+        cudaStream_t st = static_cast<cudaStream_t>(stream);
+        if (!rc) {
+            if (!msc->sky_recorded)
+                CU(cudaEventRecord(msc->sky_ev, st));
+            CU(cudaMemsetAsync(msc->prog + 2 * msc->prog_chunks, 0x01, sizeof(unsigned) * msc->prog_chunks, st));
+        }
+        msc->prog = nullptr; // one-shot
+    }
+    return rc;
+}
+
+static int render_device_impl(const RtcScene *sc, const Scene *sky, const Camera *cam, const RtcDeviceJob *job,
+                              uint8_t *d_rgb, float *d_accum, int32_t *d_ids, uint64_t *d_stats, void *stream)
 {
     int rc = check_job(sc, sky, cam, job);
     if (rc)
@@ -694,8 +724,17 @@ int rtc_render_device(const RtcScene *sc, const Scene *sky, const Camera *cam, c
                        (job->out_h + 4 * rtc::BLK_H * rtc::SKYB_WARPS - 1) / (4 * rtc::BLK_H * rtc::SKYB_WARPS), planes);
             CU(cudaFuncSetAttribute(rtc::render_skyblock_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)bsmem));
+            if (msc->prog && job->nsplit <= 1 && d_rgb) {
+                a.prog = msc->prog;
+                a.prog_rows = msc->prog_rows;
+                a.prog_chunks = msc->prog_chunks;
+            }
             rtc::render_skyblock_kernel<<<bgrid, rtc::SKYB_THREADS, bsmem, st>>>(a, msc->tab, sw);
             CU(cudaGetLastError());
+            if (a.prog) { // sky pixels are final; hit pixels follow chunk by chunk from the path kernel
+                CU(cudaEventRecord(msc->sky_ev, st));
+                msc->sky_recorded = true;
+            }
             if (timed)
                 CU(cudaEventRecord(msc->kev[1], st));
             {
@@ -882,7 +921,27 @@ struct DeviceSlot {
     size_t img_bytes = 0;
     float *accum = nullptr; // tile split with nsplit > 1: local sub-stream planes
     size_t accum_bytes = 0;
+    // single-GPU frames: the image goes to the host in row chunks, each as soon as its pixels are final
+    cudaStream_t copy = nullptr;
+    unsigned *prog = nullptr; // 3 * COPY_CHUNKS words, see RenderArgs::prog
 };
+
+constexpr int COPY_CHUNKS = 16;
+using WaitValue32Fn = int (*)(cudaStream_t, unsigned long long, unsigned, unsigned); // cuStreamWaitValue32
+WaitValue32Fn wait_value32()
+{
+    static WaitValue32Fn fn = []() -> WaitValue32Fn {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess) {
+            cudaGetLastError();
+            return nullptr;
+        }
+        return reinterpret_cast<WaitValue32Fn>(p);
+    }();
+    return fn;
+}
 
 struct Context {
     std::mutex mu;
@@ -961,6 +1020,9 @@ extern "C" void render_cuda_shutdown(void)
         cudaFree(s.stats);
         cudaFree(s.img);
         cudaFree(s.accum);
+        cudaFree(s.prog);
+        if (s.copy)
+            cudaStreamDestroy(s.copy);
         s = DeviceSlot();
     }
 }
@@ -1048,6 +1110,8 @@ int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const
     else
         part_bytes = (size_t)job[0].out_h * W * 3; // device 0 owns the most rows
 
+    bool pipelined = false;
+    int chunk_rows = 0;
     // launch everything, device by device (all asynchronous)
     for (int g = 0; g < G; ++g) {
         int dev = base + g;
@@ -1068,6 +1132,22 @@ int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const
         if (g == 0 && G > 1)
             if ((rc = ensure(reinterpret_cast<void **>(&s.img), &s.img_bytes, img_bytes)))
                 return rc;
+        // one GPU, plain frame: the device->host copy runs chunk by chunk on its own stream, behind the kernels
+        pipelined = G == 1 && S == 1 && !samples && H >= 8 * COPY_CHUNKS && wait_value32() != nullptr &&
+                    getenv("RTC_NO_PIPELINE") == nullptr;
+        if (pipelined) {
+            if (!s.copy)
+                CU(cudaStreamCreateWithFlags(&s.copy, cudaStreamNonBlocking));
+            if (!s.prog)
+                CU(cudaMalloc(&s.prog, sizeof(unsigned) * 3 * COPY_CHUNKS));
+            if (!s.scene->sky_ev)
+                CU(cudaEventCreateWithFlags(&s.scene->sky_ev, cudaEventDisableTiming));
+            CU(cudaMemsetAsync(s.prog, 0, sizeof(unsigned) * 3 * COPY_CHUNKS, s.stream));
+            chunk_rows = ((H + COPY_CHUNKS - 1) / COPY_CHUNKS + 7) / 8 * 8; // whole 8 x 4 pixel blocks
+            s.scene->prog = s.prog;
+            s.scene->prog_rows = chunk_rows;
+            s.scene->prog_chunks = COPY_CHUNKS;
+        }
         CU(cudaEventRecord(s.ev[0], s.stream));
         CU(cudaMemsetAsync(s.stats, 0, sizeof(unsigned long long) * RTC_DEVICE_STATS_WORDS, s.stream));
         if ((rc = scene_upload(s.scene, p->tris, p->ntris, p->spheres, p->nspheres, s.stream)))
@@ -1118,7 +1198,23 @@ int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const
     }
     CU(cudaSetDevice(base));
     CU(cudaEventRecord(s0.ev[3], s0.stream));
-    CU(cudaMemcpyAsync(out_rgb, d_final, img_bytes, cudaMemcpyDeviceToHost, s0.stream));
+    if (pipelined) {
+        // the copy stream follows the kernels: sky pixels are final after the classification kernel, the rows of
+        // a chunk once the path kernel has finished its last primary-hit pixel (flag set on the device;
+        // rtc_render_device sets every flag at the end of the frame whatever path it took)
+        CU(cudaStreamWaitEvent(s0.copy, s0.scene->sky_ev, 0));
+        for (int c = 0; c < COPY_CHUNKS; ++c) {
+            const size_t r0 = (size_t)c * chunk_rows;
+            if (r0 >= (size_t)H)
+                break;
+            const size_t r1 = std::min<size_t>((size_t)H, r0 + chunk_rows);
+            if (wait_value32()(s0.copy, (unsigned long long)(uintptr_t)(s0.prog + 2 * COPY_CHUNKS + c), 1u, 0u /* GEQ */) != 0)
+                return fail(RTC_ERR_CUDA, "cuStreamWaitValue32 failed");
+            CU(cudaMemcpyAsync(out_rgb + r0 * W * 3, d_final + r0 * W * 3, (r1 - r0) * W * 3, cudaMemcpyDeviceToHost, s0.copy));
+        }
+    } else {
+        CU(cudaMemcpyAsync(out_rgb, d_final, img_bytes, cudaMemcpyDeviceToHost, s0.stream));
+    }
 
     // ids and counters
     std::vector<int32_t> tmp;
@@ -1129,6 +1225,8 @@ int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const
         DeviceSlot &s = g_ctx.slot[dev];
         CU(cudaSetDevice(dev));
         CU(cudaStreamSynchronize(s.stream));
+        if (pipelined)
+            CU(cudaStreamSynchronize(s.copy));
         unsigned long long h[RTC_DEVICE_STATS_WORDS];
         CU(cudaMemcpy(h, s.stats, sizeof h, cudaMemcpyDeviceToHost));
         for (int i = 0; i < RTC_DEVICE_STATS_WORDS; ++i)

@@ -395,6 +395,8 @@ __global__ void RTC_PATH_BOUNDS render_paths_kernel(const RenderArgs a, const Pa
 
     const unsigned npix = w.list ? *w.list_count : (unsigned)(a.out_w * a.out_h);
     const unsigned total = npix * (unsigned)w.planes;
+    if (a.prog != nullptr && blockIdx.x == 0 && (int)threadIdx.x < a.prog_chunks && a.prog[threadIdx.x] == 0)
+        *(volatile unsigned *)&a.prog[2 * a.prog_chunks + threadIdx.x] = 1u; // chunks without hit pixels are final already
     // Group mode: with fewer tasks than lanes (a frame split over many GPUs, a small image) S lanes share one
     // pixel.  They hold identical state (same task, same deterministic shading), each sweeps the triangles
     // j = r, r + S, ... and the group takes the (distance, index) minimum: the pixel's serial chain, which bounds
@@ -447,6 +449,14 @@ __global__ void RTC_PATH_BOUNDS render_paths_kernel(const RenderArgs a, const Pa
                 p[0] = (uint8_t)float_to_uint8(L.acc.x);
                 p[1] = (uint8_t)float_to_uint8(L.acc.y);
                 p[2] = (uint8_t)float_to_uint8(L.acc.z);
+                if (a.prog != nullptr) { // the chunk's last finished pixel releases its rows to the copy engine
+                    const int c = (pix / a.out_w) / a.prog_rows, K = a.prog_chunks;
+                    __threadfence();
+                    if (atomicAdd(&a.prog[K + c], 1u) + 1u == a.prog[c]) {
+                        __threadfence_system();
+                        *(volatile unsigned *)&a.prog[2 * K + c] = 1u;
+                    }
+                }
             }
         } else {
             L.pos = a.origin;

@@ -46,6 +46,11 @@ struct RenderArgs {
     float *accum;       // [planes][out_h][out_w][3] or null
     int32_t *ids;       // [out_h][out_w] or null
     unsigned long long *stats; // RTC_DEVICE_STATS_WORDS or null
+    // Row-chunk completion for the pipelined device->host copy (render_cuda): prog[0..K) = primary-hit pixels per
+    // chunk of prog_rows output rows (counted by the classification), [K..2K) = finished ones (path kernel),
+    // [2K..3K) = flags set to 1 when a chunk's pixels are all final.  null: not tracked.
+    unsigned *prog;
+    int prog_rows, prog_chunks;
 };
 
 // stats words

@@ -287,6 +287,8 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
                             incl += v;
                     }
                     const unsigned tot = __shfl_sync(0xffffffffu, incl, 31);
+                    if (a.prog != nullptr && cnt) // prog_rows is a multiple of the block height: one chunk per block
+                        atomicAdd(&a.prog[cj0 / a.prog_rows], cnt);
                     if (tot) {
                         unsigned base = 0;
                         if (lane == 31)
