@@ -417,19 +417,30 @@ def run_ours(a) -> dict:
         "frame_ms": ms_per_step,
     }
     # roofline of the dominant kernel.  The path kernel is the brute-force intersection kernel proper: every
-    # (bounce ray, triangle) pair runs the reference's arithmetic (non-contracted FMUL/FADD).  The primary kernel
-    # decides most pairs with conservative block bounds, so its algorithmic rate is not bounded by the FP32 peak.
+    # (bounce ray, triangle) pair goes through its conservative quick test (FMUL/FFMA chains) and the survivors
+    # through the reference's arithmetic (non-contracted FMUL/FADD).  The primary kernel decides most pairs with
+    # conservative block bounds, so its algorithmic rate is not bounded by the FP32 peak.
+    # traffic: DRAM bytes per launch of that kernel from the committed ncu --set full capture of this workload
+    # (profiles/ncu_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum), null when there is none.
+    traffic = {}
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            traffic = json.load(f).get(wl, {})
+    except OSError:
+        pass
+
     def roof(kernel, ms, staged, brute, pairs, note):
+        tr = next((v for k, v in traffic.items() if k in kernel), None)
         return {"bound": "fp32", "unit": "TFLOP/s", "kernel": kernel, "kernel_ms": ms,
                 "achieved": staged / (ms * 1e-3) / 1e12, "peak": peak_tflops,
-                "frac": staged / (ms * 1e-3) / 1e12 / peak_tflops, "traffic": None,
+                "frac": staged / (ms * 1e-3) / 1e12 / peak_tflops, "traffic": tr,
                 "brute_force_frac": brute / (ms * 1e-3) / 1e12 / peak_tflops,
                 "pairs_per_s": pairs / (ms * 1e-3), "what": note}
     what = ("algorithmic FP32 flops of this kernel's (ray, triangle) pairs by the reference's own exits "
             "(5/19/29/45/51 per pair, SURVEY 8d) / its CUDA-event time; peak = dependent-free FFMA probe measured in "
             "this run (2 flop x FFMA/s; MEASURED_PEAKS.json has no FP32 entry); brute_force_frac = 51 flop x pairs")
     if path_ms and prim_ms:
-        rp = roof("rtc::render_paths_kernel (bounce rays: exact brute-force sweep + shading)", path_ms, staged_bounce,
+        rp = roof("rtc::render_paths_kernel (bounce rays: brute-force sweep, conservative quick test + exact survivors, + shading)", path_ms, staged_bounce,
                   brute_bounce, float(st_b[1]), what)
         rq = roof("primary kernel (rtc::render_skyblock_kernel / render_sky_kernel: conservative bounds + exact "
                   "survivors, every primary ray every sample)", prim_ms, staged_primary, brute_primary, float(st_p[1]),

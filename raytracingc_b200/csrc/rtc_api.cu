@@ -683,7 +683,8 @@ static int render_device_impl(const RtcScene *sc, const Scene *sky, const Camera
         if (sc->ntris > msc->cap_tab || !msc->tab) {
             CU(cudaFree(msc->tab));
             msc->tab = nullptr;
-            CU(cudaMalloc(&msc->tab, sizeof(float4) * 4 * (size_t)(sc->ntris > 0 ? sc->ntris : 1)));
+            CU(cudaMalloc(&msc->tab, sizeof(float4) * rtc::TAB_F4 * (size_t)(sc->ntris > 0 ? sc->ntris : 1)));
+            CU(cudaMemsetAsync(msc->tab, 0, sizeof(float4) * rtc::TAB_F4 * (size_t)(sc->ntris > 0 ? sc->ntris : 1), st));
             msc->cap_tab = sc->ntris > 0 ? sc->ntris : 1;
         }
         const int nsph_eff = job->trianglesOnly ? 0 : sc->nsph;

@@ -24,6 +24,11 @@
 
 namespace rtc {
 
+// float4 per triangle in the edge-function table: 4 edge functions + 1 pad.  The 80-byte stride makes the
+// lane-per-triangle loads of the warp-level bound (lane j reads entry j) conflict-free in shared memory
+// (a 64-byte stride puts every other lane of a quarter-warp on the same four banks).
+constexpr int TAB_F4 = 5;
+
 struct PrimaryFrame {
     f3 origin, ex, ey, ez;
     float fov;
@@ -119,7 +124,7 @@ __global__ void prepare_primary_kernel(const DeviceScene sc, const PrimaryFrame 
         }
     }
     for (int k = 0; k < 4; ++k)
-        tab[4 * i + k] = out[k];
+        tab[TAB_F4 * i + k] = out[k];
 }
 
 // ---- spheres: conservative bound of the discriminant over a pixel block ---------------------------------------

@@ -39,7 +39,7 @@ struct SkyWork {
 __host__ __device__ inline size_t sky_smem_bytes(int ntris, bool stream)
 {
     const int n = stream ? 2 * SKY_TILE : (ntris > 0 ? ntris : 1);
-    return (size_t)n * 4 * sizeof(float4);
+    return (size_t)n * TAB_F4 * sizeof(float4);
 }
 
 template <int R>
@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(FAST_THREADS) render_sky_kernel(const RenderAr
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
     if (!stream) {
-        for (int i = threadIdx.x; i < 4 * ntris; i += FAST_THREADS)
+        for (int i = threadIdx.x; i < TAB_F4 * ntris; i += FAST_THREADS)
             sF[i] = tab[i];
     } else if (threadIdx.x == 0) {
         mbar_init(&bars[0], 1);
@@ -90,10 +90,10 @@ __global__ void __launch_bounds__(FAST_THREADS) render_sky_kernel(const RenderAr
 
     auto issue = [&](uint32_t k, int t) {
         const int n = min(tile, ntris - t * tile);
-        const uint32_t bytes = (uint32_t)n * 4u * (uint32_t)sizeof(float4);
+        const uint32_t bytes = (uint32_t)n * (uint32_t)TAB_F4 * (uint32_t)sizeof(float4);
         fence_proxy_async();
         mbar_arrive_expect_tx(&bars[k & 1], bytes);
-        tma_load_1d(sF + (size_t)(k & 1) * SKY_TILE * 4, tab + (size_t)t * tile * 4, bytes, &bars[k & 1]);
+        tma_load_1d(sF + (size_t)(k & 1) * SKY_TILE * TAB_F4, tab + (size_t)t * tile * TAB_F4, bytes, &bars[k & 1]);
     };
 
     for (int s = s0; s < s1; ++s) {
@@ -125,14 +125,14 @@ __global__ void __launch_bounds__(FAST_THREADS) render_sky_kernel(const RenderAr
             if (stream) {
                 const uint32_t k = k0 + (uint32_t)t;
                 mbar_wait(&bars[k & 1], (k >> 1) & 1u);
-                F = sF + (size_t)(k & 1) * SKY_TILE * 4;
+                F = sF + (size_t)(k & 1) * SKY_TILE * TAB_F4;
                 n = min(tile, ntris - t * tile);
                 base = t * tile;
             }
             if (warp_busy) {
 #pragma unroll 2
                 for (int i = 0; i < n; ++i) {
-                    const float4 f0 = F[4 * i], f1 = F[4 * i + 1], f2 = F[4 * i + 2], f3_ = F[4 * i + 3];
+                    const float4 f0 = F[TAB_F4 * i], f1 = F[TAB_F4 * i + 1], f2 = F[TAB_F4 * i + 2], f3_ = F[TAB_F4 * i + 3];
                     float e0 = fmaf(f0.x, dx0, fmaf(f0.y, dy, f0.z));
                     float e1 = fmaf(f1.x, dx0, fmaf(f1.y, dy, f1.z));
                     float e2 = fmaf(f2.x, dx0, fmaf(f2.y, dy, f2.z));

@@ -45,11 +45,11 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
     const int ntiles = (ntris + tile - 1) / tile;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float4 *sF = smem_dyn;
-    float2 *hitbuf = reinterpret_cast<float2 *>(sF + (stream ? 2 * SKY_TILE * 4 : 4 * (ntris > 0 ? ntris : 1))) +
+    float2 *hitbuf = reinterpret_cast<float2 *>(sF + (stream ? 2 * SKY_TILE * TAB_F4 : TAB_F4 * (ntris > 0 ? ntris : 1))) +
                      (size_t)warp * 32 * 32; // [lane-block][pixel] {best, id}
 
     if (!stream) {
-        for (int i = threadIdx.x; i < 4 * ntris; i += SKYB_THREADS)
+        for (int i = threadIdx.x; i < TAB_F4 * ntris; i += SKYB_THREADS)
             sF[i] = tab[i];
     } else if (threadIdx.x == 0) {
         mbar_init(&bars[0], 1);
@@ -93,10 +93,10 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
 
     auto issue = [&](uint32_t k, int t) {
         const int n = min(tile, ntris - t * tile);
-        const uint32_t bytes = (uint32_t)n * 4u * (uint32_t)sizeof(float4);
+        const uint32_t bytes = (uint32_t)n * (uint32_t)TAB_F4 * (uint32_t)sizeof(float4);
         fence_proxy_async();
         mbar_arrive_expect_tx(&bars[k & 1], bytes);
-        tma_load_1d(sF + (size_t)(k & 1) * SKY_TILE * 4, tab + (size_t)t * tile * 4, bytes, &bars[k & 1]);
+        tma_load_1d(sF + (size_t)(k & 1) * SKY_TILE * TAB_F4, tab + (size_t)t * tile * TAB_F4, bytes, &bars[k & 1]);
     };
 
     for (int s = s0; s < s1; ++s) {
@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
             if (stream) {
                 const uint32_t k = k0 + (uint32_t)t;
                 mbar_wait(&bars[k & 1], (k >> 1) & 1u);
-                F = sF + (size_t)(k & 1) * SKY_TILE * 4;
+                F = sF + (size_t)(k & 1) * SKY_TILE * TAB_F4;
                 n = min(tile, ntris - t * tile);
                 tbase = t * tile;
             }
@@ -169,7 +169,7 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
                     // ---- level 1: lane j bounds triangle c0 + j over the WARP's whole 64 x 16 pixel region ----
                     bool wpass = false;
                     if (lane < cn) {
-                        const float4 *f = F + 4 * (c0 + lane);
+                        const float4 *f = F + TAB_F4 * (c0 + lane);
                         const float4 f0 = f[0], f1 = f[1], f2 = f[2], f3_ = f[3];
                         const float e0 = fmaf(fabsf(f0.x), ehw, fmaf(fabsf(f0.y), ehh, fmaf(f0.x, wcx, fmaf(f0.y, wcy, f0.z))));
                         const float e1 = fmaf(fabsf(f1.x), ehw, fmaf(fabsf(f1.y), ehh, fmaf(f1.x, wcx, fmaf(f1.y, wcy, f1.z))));
@@ -184,7 +184,7 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
                     while (wm) {
                         const int j = __ffs(wm) - 1;
                         wm &= wm - 1;
-                        const float4 *f = F + 4 * (c0 + j);
+                        const float4 *f = F + TAB_F4 * (c0 + j);
                         const float4 f0 = f[0], f1 = f[1], f2 = f[2], f3_ = f[3];
                         const float e0 = fmaf(f0.x, cx, fmaf(f0.y, cy, f0.z));
                         const float e1 = fmaf(f1.x, cx, fmaf(f1.y, cy, f1.z));
@@ -226,7 +226,7 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
                             const int j = __ffs(m) - 1;
                             m &= m - 1;
                             const int ti = tbase + c0 + j;
-                            const float4 *f = F + 4 * (c0 + j);
+                            const float4 *f = F + TAB_F4 * (c0 + j);
                             const float4 f0 = f[0], f1 = f[1], f2 = f[2], f3_ = f[3];
                             const float t0 = fmaf(f0.x, dxr, fmaf(f0.y, dyr, f0.w));
                             const float t1 = fmaf(f1.x, dxr, fmaf(f1.y, dyr, f1.w));
@@ -400,7 +400,7 @@ __global__ void __launch_bounds__(BTASK_THREADS) render_blocktask_kernel(const R
     const int ntiles = (ntris + tile - 1) / tile;
     const int lane = threadIdx.x & 31;
     if (!stream) {
-        for (int i = threadIdx.x; i < 4 * ntris; i += BTASK_THREADS)
+        for (int i = threadIdx.x; i < TAB_F4 * ntris; i += BTASK_THREADS)
             sF[i] = tab[i];
     } else if (threadIdx.x == 0) {
         mbar_init(&bars[0], 1);
@@ -416,10 +416,10 @@ __global__ void __launch_bounds__(BTASK_THREADS) render_blocktask_kernel(const R
     auto dy_at = [&](int cj) { return xdiv((float)(y_of(cj) - a.H / 2), fh); };
     auto issue = [&](uint32_t k, int t) {
         const int n = min(tile, ntris - t * tile);
-        const uint32_t bytes = (uint32_t)n * 4u * (uint32_t)sizeof(float4);
+        const uint32_t bytes = (uint32_t)n * (uint32_t)TAB_F4 * (uint32_t)sizeof(float4);
         fence_proxy_async();
         mbar_arrive_expect_tx(&bars[k & 1], bytes);
-        tma_load_1d(sF + (size_t)(k & 1) * SKY_TILE * 4, tab + (size_t)t * tile * 4, bytes, &bars[k & 1]);
+        tma_load_1d(sF + (size_t)(k & 1) * SKY_TILE * TAB_F4, tab + (size_t)t * tile * TAB_F4, bytes, &bars[k & 1]);
     };
 
     // task state (warp-uniform except the per-pixel values)
@@ -476,7 +476,7 @@ __global__ void __launch_bounds__(BTASK_THREADS) render_blocktask_kernel(const R
             if (stream) {
                 const uint32_t k = k0 + (uint32_t)t;
                 mbar_wait(&bars[k & 1], (k >> 1) & 1u);
-                F = sF + (size_t)(k & 1) * SKY_TILE * 4;
+                F = sF + (size_t)(k & 1) * SKY_TILE * TAB_F4;
                 n = min(tile, ntris - t * tile);
                 tbase = t * tile;
             }
@@ -484,7 +484,7 @@ __global__ void __launch_bounds__(BTASK_THREADS) render_blocktask_kernel(const R
                 for (int c0 = 0; c0 < n; c0 += 32) {
                     bool bpass = false;
                     if (c0 + lane < n) {
-                        const float4 *f = F + 4 * (c0 + lane);
+                        const float4 *f = F + TAB_F4 * (c0 + lane);
                         const float4 f0 = f[0], f1 = f[1], f2 = f[2], f3_ = f[3];
                         const float e0 = fmaf(f0.x, cx, fmaf(f0.y, cy, f0.z));
                         const float e1 = fmaf(f1.x, cx, fmaf(f1.y, cy, f1.z));
@@ -497,7 +497,7 @@ __global__ void __launch_bounds__(BTASK_THREADS) render_blocktask_kernel(const R
                         const int j = __ffs(m) - 1;
                         m &= m - 1;
                         const int ti = tbase + c0 + j;
-                        const float4 *f = F + 4 * (c0 + j);
+                        const float4 *f = F + TAB_F4 * (c0 + j);
                         const float4 f0 = f[0], f1 = f[1], f2 = f[2], f3_ = f[3];
                         const float t0 = fmaf(f0.x, dxr, fmaf(f0.y, dyr, f0.w));
                         const float t1 = fmaf(f1.x, dxr, fmaf(f1.y, dyr, f1.w));
