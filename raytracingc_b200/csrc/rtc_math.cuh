@@ -108,13 +108,18 @@ __device__ __forceinline__ float random_normal(uint32_t &state)
     return (float)__dmul_rn((double)rho, cos((double)theta));
 }
 // RandomDiretion (moremath.c:105-109): x, then y, then z, then normalized.
-// The call unit of the FP64 island: state in, {direction, state bits} out, all in registers; the three
-// deviates are inlined side by side so their log / cos / sqrt chains overlap.
+// The call unit of the FP64 island: state in, {direction, state bits} out, all in registers.
 __device__ __noinline__ float4 random_direction(uint32_t state)
 {
-    float x = random_normal(state);
-    float y = random_normal(state);
-    float z = random_normal(state);
+    // one copy of the FP64 code executed three times: the smaller instruction footprint beats the overlap of three
+    // inlined chains (measured, C4 path kernel: 4.15 -> 3.95 ms; the shading code is instruction-fetch bound)
+    float x = 0.f, y = 0.f, z = 0.f;
+#pragma unroll 1
+    for (int i = 0; i < 3; ++i) {
+        x = y;
+        y = z;
+        z = random_normal(state);
+    }
     f3 v = xnormalize(mk3(x, y, z));
     return make_float4(v.x, v.y, v.z, __uint_as_float(state));
 }
