@@ -10,6 +10,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import sys
 from dataclasses import dataclass, field
 
 import numpy as np
@@ -101,6 +102,14 @@ def load_library() -> C.CDLL:
     if not os.path.exists(LIB_PATH):
         raise FileNotFoundError(f"{LIB_PATH} not built: run `python -m raytracingc_b200.build` "
                                 "(there is no CPU fallback)")
+    if not os.environ.get("RTC_NCCL_LIB"):
+        # render_cuda(ngpus > 1) dlopens NCCL: make it the copy torch is linked against, so that whichever of the
+        # two is loaded first the process holds ONE libnccl.so.2
+        for d in sys.path:
+            cand = os.path.join(d, "nvidia", "nccl", "lib", "libnccl.so.2")
+            if os.path.exists(cand):
+                os.environ["RTC_NCCL_LIB"] = cand
+                break
     lib = C.CDLL(LIB_PATH)
     P = C.POINTER
     lib.render_cuda.argtypes = [P(Scene), P(Camera), C.c_void_p, P(RenderParams)]

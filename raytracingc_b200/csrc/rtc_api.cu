@@ -890,9 +890,12 @@ struct NcclApi {
     {
         if (h)
             return true;
-        const char *names[] = {"libnccl.so.2", "libnccl.so"};
+        // RTC_NCCL_LIB: the NCCL the rest of the process uses (a Python caller points it at the copy bundled with
+        // torch: a process that loads two libnccl.so.2 of different versions resolves the second one's users
+        // against the first)
+        const char *names[] = {getenv("RTC_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
         for (const char *n : names)
-            if ((h = dlopen(n, RTLD_NOW | RTLD_LOCAL)))
+            if (n && *n && (h = dlopen(n, RTLD_NOW | RTLD_LOCAL)))
                 break;
         if (!h)
             return false;
