@@ -524,6 +524,7 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
     w.planes = planes;
     w.write_ids = write_ids;
     w.coop = env_int("RTC_NO_COOP", 0) == 0;
+    w.spec = env_int("RTC_NO_SPEC", 0) == 0;
     w.tile = env_int("RTC_PATH_TILE", rtc::PATH_TILE);
     if (w.tile < 1 || w.tile > rtc::PATH_TILE)
         w.tile = rtc::PATH_TILE;
@@ -532,18 +533,30 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
     const size_t smem = rtc::path_smem_bytes(sc->ntris, stream, mode);
     int per_sm = 0;
     using PathKernel = void (*)(const rtc::RenderArgs, const rtc::PathWork);
-    static const PathKernel kernels[2][3] = {
-        {rtc::render_paths_kernel<false, 0>, rtc::render_paths_kernel<false, 1>, rtc::render_paths_kernel<false, 2>},
-        {rtc::render_paths_kernel<true, 0>, rtc::render_paths_kernel<true, 1>, rtc::render_paths_kernel<true, 2>}};
-    const PathKernel kern = kernels[stream ? 1 : 0][mode];
+    // [groups][stream][mode]: both group variants are launched, the device picks (see the kernel)
+    static const PathKernel kernels[2][2][3] = {
+        {{rtc::render_paths_kernel<false, 0, false>, rtc::render_paths_kernel<false, 1, false>, rtc::render_paths_kernel<false, 2, false>},
+         {rtc::render_paths_kernel<true, 0, false>, rtc::render_paths_kernel<true, 1, false>, rtc::render_paths_kernel<true, 2, false>}},
+        {{rtc::render_paths_kernel<false, 0, true>, rtc::render_paths_kernel<false, 1, true>, rtc::render_paths_kernel<false, 2, true>},
+         {rtc::render_paths_kernel<true, 0, true>, rtc::render_paths_kernel<true, 1, true>, rtc::render_paths_kernel<true, 2, true>}}};
+    const PathKernel kern = kernels[0][stream ? 1 : 0][mode], kern_groups = kernels[1][stream ? 1 : 0][mode];
     CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CU(cudaFuncSetAttribute(kern_groups, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // one grid size for both (the group decision compares the task count with it): the occupancy of the common kernel
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, rtc::PATH_THREADS, smem));
     if (per_sm < 1)
         return fail(RTC_ERR_CUDA, "path kernel does not fit on an SM (smem %zu)", smem);
     long long tasks = (long long)a.out_w * a.out_h * planes; // upper bound when a list is used
     long long want = (tasks + rtc::PATH_THREADS - 1) / rtc::PATH_THREADS;
     int blocks = (int)std::min<long long>((long long)sc->nsm * per_sm, want > 0 ? want : 1);
+    int per_sm_g = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_g, kern_groups, rtc::PATH_THREADS, smem));
+    if (per_sm_g < 1)
+        return fail(RTC_ERR_CUDA, "path kernel (group mode) does not fit on an SM (smem %zu)", smem);
+    const int blocks_g = sc->nsm * std::min(per_sm_g, rtc::PATH_GROUP_CTAS);
+    w.group_lanes = (unsigned)blocks_g * rtc::PATH_THREADS;
     kern<<<blocks, rtc::PATH_THREADS, smem, st>>>(a, w);
+    kern_groups<<<blocks_g, rtc::PATH_THREADS, smem, st>>>(a, w);
     CU(cudaGetLastError());
     return RTC_OK;
 }
@@ -609,7 +622,8 @@ int rtc_render_launch_count(const RtcScene *sc, const RtcDeviceJob *job, int wan
     (void)want_ids;
     if (!job || job->out_w <= 0 || job->out_h <= 0)
         return 0;
-    return 4; // prepare_primary + block kernel + block-task kernel + path kernel (other modes launch 1-3)
+    return 5; // prepare_primary + block kernel + block-task kernel + the two path-kernel instantiations, one of
+              // which returns at once (other modes launch 1-3)
 }
 
 static int render_device_impl(const RtcScene *sc, const Scene *sky, const Camera *cam, const RtcDeviceJob *job,

@@ -22,13 +22,14 @@
 namespace rtc {
 
 constexpr int PATH_THREADS = 128;
+constexpr int PATH_GROUP_CTAS = 5; // CTAs per SM of the group-mode instantiation
 #ifndef RTC_QUICK_UNROLL
 #define RTC_QUICK_UNROLL 4 // pairs per iteration of the branch-free first phase; A/B knob
 #endif
 #ifdef RTC_PATH_MINBLOCKS // min resident CTAs per SM asked of the compiler (register cap); A/B knob
-#define RTC_PATH_BOUNDS __launch_bounds__(PATH_THREADS, RTC_PATH_MINBLOCKS)
+#define RTC_PATH_MINB RTC_PATH_MINBLOCKS
 #else
-#define RTC_PATH_BOUNDS __launch_bounds__(PATH_THREADS)
+#define RTC_PATH_MINB 0
 #endif
 constexpr int PATH_TILE = 128; // triangles per streamed tile: 14 KB per stage (quick records + geometry), 2 stages
 
@@ -40,6 +41,8 @@ struct PathWork {
     int write_ids;              // 1: this kernel owns the primary-id map (no sky kernel ran)
     int tile;                   // triangles per streamed tile (<= PATH_TILE), STREAM only
     int coop;                   // 1: cooperative sweep of the last live lanes (0 only for A/B measurements)
+    unsigned group_lanes;       // lanes of the group-mode instantiation's grid (both instantiations decide with it)
+    int spec;                   // 1: group mode runs S consecutive samples of a pixel at once (see the kernel)
     const float4 *qrec;         // MODE >= 1: quick records (4 x float4 per triangle), built by quick_records_kernel
     float obound;               // MODE >= 1: the records are valid for ray origins with max |o_i| <= obound
     const float2 *rec;          // with a list: {distance, id bits} of each listed pixel's primary hit, found by the
@@ -367,9 +370,20 @@ __device__ __forceinline__ void coop_tile(CoopCtx &c, const float4 *S_, const fl
     }
 }
 
-template <bool STREAM, int MODE>
-__global__ void RTC_PATH_BOUNDS render_paths_kernel(const RenderArgs a, const PathWork w)
+// GROUPS: the instantiation for frames with fewer tasks than half the lanes (group mode, S > 1).  The host launches
+// both instantiations; each reads the task count on the device and the one it is not meant for returns at once, so
+// the common case (S = 1) runs a kernel without the group-mode state in its registers.
+// (the group instantiation is capped at the registers of PATH_GROUP_CTAS CTAs per SM and launched with exactly that
+// grid: its S is chosen for a fully resident grid)
+template <bool STREAM, int MODE, bool GROUPS>
+__global__ void __launch_bounds__(PATH_THREADS, GROUPS ? PATH_GROUP_CTAS : RTC_PATH_MINB) render_paths_kernel(const RenderArgs a, const PathWork w)
 {
+    {
+        const unsigned np = w.list ? *w.list_count : (unsigned)(a.out_w * a.out_h);
+        const bool groups = w.coop && (unsigned long long)np * (unsigned)w.planes * 2ull <= (unsigned long long)w.group_lanes;
+        if (groups != GROUPS)
+            return;
+    }
     extern __shared__ float4 sGeo[];
     // shared memory (per stage when streaming): [quick records, 4 float4 per triangle (MODE >= 1)][geometry, 3 per triangle]
     constexpr int RS = path_rec_f4(MODE), QS = RS - 3;
@@ -402,10 +416,33 @@ __global__ void RTC_PATH_BOUNDS render_paths_kernel(const RenderArgs a, const Pa
     // j = r, r + S, ... and the group takes the (distance, index) minimum: the pixel's serial chain, which bounds
     // the kernel when every lane has at most one task, gets ~S times shorter in its sweep part.
     int S = 1;
-    if (w.coop)
-        while (S < 32 && (unsigned long long)total * (unsigned)(2 * S) <= (unsigned long long)gridDim.x * PATH_THREADS)
+    if (GROUPS)
+        while (S < 32 && (unsigned long long)total * (unsigned)(2 * S) <= (unsigned long long)w.group_lanes)
             S *= 2;
     const int gr = lane & (S - 1), gbase = lane & ~(S - 1);
+    // Sample-parallel group mode (pixels whose primary hit is known): the S lanes run S CONSECUTIVE samples of the
+    // pixel at once.  A sample whose path has exactly one hit-bounce draws exactly 7 random numbers (6 for the
+    // direction, 1 for the roulette, moremath.c:98-109, raytracing.c:274-285), so lane r starts sample b + r from
+    // the batch's base state advanced by 7 r steps of the LCG (a jump: state * M_r + C_r).  When all lanes have
+    // finished, the batch is validated in order: samples up to and including the first one with more than one
+    // hit-bounce started from the right state; their contributions are added in sample order (the reference's
+    // float sum), the base state becomes that lane's final state, and everything after it is recomputed in the next
+    // batch.  Nothing speculative is ever written.  Two failed batches in a row (a closed scene) switch the pixel
+    // back to one sample at a time.
+    const bool spec = GROUPS && S > 1 && w.rec != nullptr && w.spec != 0;
+    uint32_t jm = 1u, jc = 0u; // 7 * gr steps of the LCG as one multiply-add
+    if (spec)
+        for (int k = 0; k < 7 * gr; ++k) {
+            jc = jc * 747796405u + 2891336453u;
+            jm *= 747796405u;
+        }
+    uint32_t bstate = 0;  // RNG state at the start of sample bsample (exact)
+    int bsample = 0;      // first sample of the current batch
+    bool parked = false;  // this lane's sample of the batch is finished (or it has none)
+    bool has_sample = false, spec_on = false;
+    int hcount = 0, fails = 0;
+    unsigned sample_rays = 0;
+    f3 contrib = mk3(0.f, 0.f, 0.f);
     const float fh = (float)(a.H / 2);
     const float wgt = (float)(1.0 / (double)a.spp); // main.c:99
 
@@ -432,11 +469,9 @@ __global__ void RTC_PATH_BOUNDS render_paths_kernel(const RenderArgs a, const Pa
         tma_load_1d(stage + QS * PATH_TILE, a.sc.geo + (size_t)t * tile * 3, bg, &bars[k & 1]);
     };
 
-    // a path has ended: accumulate it (main.c:99) and start the next sample, or finish the pixel
-    auto finish_sample = [&]() {
-        L.acc = xadd3(L.acc, xscale3(L.light, wgt));
-        L.sample++;
-        if (L.sample >= s_end) {
+    // the pixel's last sample is accumulated: write it
+    auto finish_pixel = [&]() {
+        {
             active = false;
             if (a.accum != nullptr && gr == 0) {
                 float *p = a.accum + ((size_t)plane * a.out_w * a.out_h + pix) * 3;
@@ -458,14 +493,41 @@ __global__ void RTC_PATH_BOUNDS render_paths_kernel(const RenderArgs a, const Pa
                     }
                 }
             }
-        } else {
-            L.pos = a.origin;
-            L.dir = pdir;
-            L.tint = mk3(1.f, 1.f, 1.f);
-            L.light = mk3(0.f, 0.f, 0.f);
-            L.bounce = 0;
-            fresh = true;
         }
+    };
+    auto reset_path = [&]() {
+        L.pos = a.origin;
+        L.dir = pdir;
+        L.tint = mk3(1.f, 1.f, 1.f);
+        L.light = mk3(0.f, 0.f, 0.f);
+        L.bounce = 0;
+        fresh = true;
+        pend = false;
+    };
+    // sample-parallel group mode: this lane's sample of the batch that starts at (bsample, bstate)
+    auto start_batch = [&]() {
+        has_sample = (spec_on || gr == 0) && bsample + gr < s_end;
+        L.sample = bsample + gr;
+        L.rng = bstate * jm + jc;
+        reset_path();
+        hcount = 0;
+        sample_rays = 0;
+        contrib = mk3(0.f, 0.f, 0.f);
+        parked = !has_sample;
+    };
+    // a path has ended: accumulate it (main.c:99) and start the next sample, or finish the pixel
+    auto finish_sample = [&]() {
+        if (spec) { // kept aside until the batch is validated
+            contrib = xscale3(L.light, wgt);
+            parked = true;
+            return;
+        }
+        L.acc = xadd3(L.acc, xscale3(L.light, wgt));
+        L.sample++;
+        if (L.sample >= s_end)
+            finish_pixel();
+        else
+            reset_path();
     };
 
     while (true) {
@@ -507,6 +569,13 @@ __global__ void RTC_PATH_BOUNDS render_paths_kernel(const RenderArgs a, const Pa
                             id0 = __float_as_int(r.y);
                         }
                         active = L.sample < s_end;
+                        if (spec && active) {
+                            bsample = L.sample;
+                            bstate = L.rng;
+                            spec_on = true;
+                            fails = 0;
+                            start_batch();
+                        }
                         if (!active) { // empty sample range: the pixel's partial sum is zero
                             if (a.accum != nullptr && gr == 0) {
                                 float *p = a.accum + ((size_t)plane * a.out_w * a.out_h + pix) * 3;
@@ -519,23 +588,59 @@ __global__ void RTC_PATH_BOUNDS render_paths_kernel(const RenderArgs a, const Pa
                 }
             }
         }
+        // ---- sample-parallel group mode: a group whose lanes have all finished their sample validates the batch
+        //      (before the shading pass, so the next batch's first hits are shaded in this round) ----
+        if (spec) {
+            const unsigned gmask = (S == 32 ? 0xffffffffu : ((1u << S) - 1u)) << gbase;
+            const unsigned pk = __ballot_sync(0xffffffffu, !active || parked);
+            const bool all = active && (pk & gmask) == gmask;
+            if (__any_sync(0xffffffffu, all)) {
+                const unsigned dev = __ballot_sync(0xffffffffu, all && has_sample && hcount != 1) & gmask;
+                const int nb = min(spec_on ? S : 1, s_end - bsample);
+                const int nvalid = dev ? min(__ffs(dev) - gbase, nb) : nb; // up to and including the first deviation
+                for (int j = 0; j < S; ++j) {
+                    const f3 c = mk3(__shfl_sync(0xffffffffu, contrib.x, gbase + j), __shfl_sync(0xffffffffu, contrib.y, gbase + j),
+                                     __shfl_sync(0xffffffffu, contrib.z, gbase + j));
+                    const unsigned r = __shfl_sync(0xffffffffu, sample_rays, gbase + j);
+                    if (all && j < nvalid) {
+                        L.acc = xadd3(L.acc, c); // main.c:99, in sample order, identically on every lane of the group
+                        nrays += gr == 0 ? r : 0u;
+                    }
+                }
+                const uint32_t endstate = __shfl_sync(0xffffffffu, L.rng, gbase + max(nvalid - 1, 0));
+                if (all) {
+                    bstate = endstate;
+                    bsample += nvalid;
+                    if (nb > 1) {
+                        fails = nvalid == 1 ? fails + 1 : 0;
+                        if (fails >= 2)
+                            spec_on = false;
+                    }
+                    if (bsample >= s_end)
+                        finish_pixel();
+                    else
+                        start_batch();
+                }
+            }
+        }
         // ---- hit shading, ONE pass per round for both kinds of pending hits: the hit the last sweep found, and the
         //      known primary hit of a lane that starts a sample (the primary kernel sweeps that ray every sample).
         //      A lane whose path ends here (Russian roulette, bounce limit) and whose next sample again starts from
         //      a known hit sits out this round's sweep: repeating the pass for those few lanes would cost a full
         //      shading pass at a few percent lane utilisation each time. ----
-        if (active && (pend || (has_rec && fresh))) {
+        if (active && !parked && (pend || (has_rec && fresh))) {
             if (!pend) {
                 best = best0;
                 bestId = id0;
             }
             pend = false;
             fresh = false;
+            hcount++;
             if (shade_hit(L, a, best, bestId))
                 finish_sample();
         }
         // lanes with a ray to sweep this round
-        const bool sweeping = active && !(has_rec && fresh);
+        const bool sweeping = active && !parked && !(has_rec && fresh);
         // a lane that finished its pixel in the pass above fetches at the top of the next round: the warp leaves
         // only when no lane has work AND the list is exhausted
         const bool live = active || !exhausted;
@@ -552,7 +657,7 @@ __global__ void RTC_PATH_BOUNDS render_paths_kernel(const RenderArgs a, const Pa
         // few live lanes and nothing left to fetch: sweep cooperatively (see CoopCtx)
         const unsigned act = __ballot_sync(0xffffffffu, sweeping);
         const int na = __popc(act);
-        const bool coop = S == 1 && na > 0 && na <= 16 && w.coop;
+        const bool coop = (S == 1 || spec) && na > 0 && na <= 16 && w.coop;
         CoopCtx cc;
         if (coop) {
             cc.S = na <= 1 ? 32 : (na <= 2 ? 16 : (na <= 4 ? 8 : (na <= 8 ? 4 : 2)));
@@ -585,7 +690,7 @@ __global__ void RTC_PATH_BOUNDS render_paths_kernel(const RenderArgs a, const Pa
                 bestId = gi;
             }
         };
-        const bool grouped = S > 1;
+        const bool grouped = S > 1 && !spec;
         if (grouped) { // the group's lanes hold the same ray; member gr sweeps every S-th triangle
             cc.S = S;
             cc.r = gr;
@@ -629,7 +734,10 @@ __global__ void RTC_PATH_BOUNDS render_paths_kernel(const RenderArgs a, const Pa
 
         // ---- shade (calcColor's loop body), advance the state machine ----
         if (sweeping) {
-            nrays += gr == 0;
+            if (spec)
+                sample_rays++; // counted when the batch validates the sample
+            else
+                nrays += gr == 0;
             if (first) {
                 first = false;
                 if (w.write_ids && plane == 0 && gr == 0) {
