@@ -39,7 +39,7 @@ extern "C" {
 
 /* ---- RenderParams.flags --------------------------------------------------- */
 #define RTC_FLAG_COUNT_EXITS 1u /* fill RenderStats.tri_exit (slower kernel)     */
-#define RTC_FLAG_EXACT_ONLY 2u  /* disable the conservative FMA pre-filter: every
+#define RTC_FLAG_EXACT_ONLY 2u  /* disable every conservative pre-filter: every
                                    ray-triangle pair runs the reference's own
                                    operation sequence (validation mode)          */
 #define RTC_FLAG_PER_PAIR_FILTER 8u /* primary pre-filter evaluated per (pixel, triangle) pair instead of

@@ -1,16 +1,20 @@
-// rtc_paths.cuh -- the path kernel: one lane = one pixel's RNG stream, exact arithmetic for every ray.
+// rtc_paths.cuh -- the path kernel: one lane = one pixel's RNG stream; every ray's result is the reference's.
 //
 // A lane is a state machine over (sample, bounce) of "its" pixel (the stream is serial per pixel: seeded once,
-// main.c:95, continuing across samples, main.c:98-99).  The warp iterates
-//     sweep the lane's current ray over ALL triangles (calculateRayCollision, raytracing.c:216-240)  ->  shade
+// main.c:95, continuing across samples, main.c:98-99).  A warp round is
+//     fetch tasks -> shade pending hits (once) -> sweep the lane's current ray over ALL triangles
+//     (calculateRayCollision, raytracing.c:216-240) -> shade misses
 // so lanes with different path lengths never wait for each other, and a lane whose pixel is finished fetches
 // the next pixel from a global work list (persistent lanes: no tail beyond one pixel's own serial chain).
 //
-// Work list: either the compact list of primary-hit pixels produced by the sky kernel (rtc_sky.cuh), or, with
-// list == nullptr, every pixel of the subset.  A task is (pixel, plane); plane = sub-stream of a sample split.
+// Work list: either the compact list of primary-hit pixels produced by the classification kernel
+// (rtc_skyblock.cuh / rtc_sky.cuh) together with each pixel's primary-hit record, or, with list == nullptr, every
+// pixel of the subset.  A task is (pixel, plane); plane = sub-stream of a sample split.
 //
-// Per-triangle data of the sweep's first phase lives in shared memory -- MODE 0: the geometry itself (48 B per
-// triangle, rtc_scene.cuh); MODE 1/2: the 64 B quick records (QuickRecord below):
+// The sweep has two phases per chunk of 32 triangles: a branch-free conservative quick test of every pair
+// (MODE 0: in the reference's arithmetic; MODE 1: from per-triangle quick records, quick_records_kernel below;
+// MODE 2: MODE 1 + verification) and the reference's exact test (tri_test_exact) on the survivors in index order.
+// Shared memory holds the geometry (48 B per triangle, rtc_scene.cuh) and, in MODE 1/2, the 64 B quick records:
 //   STREAM = false  the whole scene is resident (loaded once per CTA); warps run independently.
 //   STREAM = true   scenes of any size: PATH_TILE-triangle tiles are streamed by the TMA unit
 //                   (cp.async.bulk + mbarrier, double-buffered); the CTA's warps sweep in lock-step.

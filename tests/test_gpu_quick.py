@@ -115,3 +115,26 @@ def test_quick_with_spheres_and_bundled_scene():
     assert (ids_v == ids_e).all() and (rgb_v == rgb_e).all()
     rgb_f, ids_f, st_f = rtc.render(tris, **kw)
     assert (rgb_f == rgb_e).all()
+
+
+@pytest.mark.parametrize("height", [128, 135, 200, 333])
+def test_pipelined_copy_matches_plain_copy(height, monkeypatch):
+    """render_cuda copies the image to the host in row chunks behind the kernels (per-chunk completion flags);
+    the result must equal the plain copy at the end of the frame, for heights that do not divide into the chunks,
+    with pageable and with page-locked host buffers."""
+    import os
+    import torch
+    import raytracingc_b200 as rtc
+    path = os.path.join(os.path.dirname(__file__), "golden", "scenes", "ultracomplex.tris")
+    tris = np.fromfile(path, dtype=rtc.TRI_DTYPE)
+    kw = dict(width=257, height=height, spp=5, max_bounce=3, triangles_only=1)
+    monkeypatch.setenv("RTC_NO_PIPELINE", "1")
+    ref, _, st0 = rtc.render(tris, **kw)
+    monkeypatch.delenv("RTC_NO_PIPELINE")
+    out, _, st1 = rtc.render(tris, **kw)
+    assert st0["rays"] == st1["rays"]
+    assert (out == ref).all()
+    pinned = torch.empty((height, 257, 3), dtype=torch.uint8).pin_memory()
+    pinned.fill_(7)
+    out2, _, _ = rtc.render(tris, out=pinned.numpy(), **kw)
+    assert (pinned.numpy() == ref).all()
