@@ -8,7 +8,10 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <mutex>
+#include <tuple>
+#include <utility>
 #include <vector>
 
 #include <cuda_runtime.h>
@@ -427,6 +430,32 @@ bool camera_is_orthonormal(const Camera *c)
 }
 
 // env override helpers (test / tuning knobs; unset in production)
+// cudaFuncSetAttribute + occupancy query of a kernel at a dynamic shared-memory size.  Both runtime calls cost
+// several microseconds and a frame makes a dozen of them, so the opt-in limit is only ever raised (it is sticky per
+// function) and the occupancy is remembered per (device, kernel, size).
+int kernel_occupancy(int device, const void *kern, int threads, size_t smem, int *per_sm)
+{
+    using FnKey = std::pair<int, const void *>;
+    static std::map<FnKey, size_t> limit;                      // opt-in shared memory currently set
+    static std::map<std::pair<FnKey, size_t>, int> occupancy;
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lk(mu);
+    const FnKey fk{device, kern};
+    auto li = limit.find(fk);
+    if (li == limit.end() || li->second < smem) {
+        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        limit[fk] = smem;
+    }
+    auto oi = occupancy.find({fk, smem});
+    if (oi == occupancy.end()) {
+        int n = 0;
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, threads, smem));
+        oi = occupancy.emplace(std::make_pair(fk, smem), n).first;
+    }
+    *per_sm = oi->second;
+    return RTC_OK;
+}
+
 int env_int(const char *name, int dflt)
 {
     const char *e = getenv(name);
@@ -540,17 +569,17 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
         {{rtc::render_paths_kernel<false, 0, true>, rtc::render_paths_kernel<false, 1, true>, rtc::render_paths_kernel<false, 2, true>},
          {rtc::render_paths_kernel<true, 0, true>, rtc::render_paths_kernel<true, 1, true>, rtc::render_paths_kernel<true, 2, true>}}};
     const PathKernel kern = kernels[0][stream ? 1 : 0][mode], kern_groups = kernels[1][stream ? 1 : 0][mode];
-    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CU(cudaFuncSetAttribute(kern_groups, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    // one grid size for both (the group decision compares the task count with it): the occupancy of the common kernel
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, rtc::PATH_THREADS, smem));
+    int rc_o = kernel_occupancy(sc->device, reinterpret_cast<const void *>(kern), rtc::PATH_THREADS, smem, &per_sm);
+    if (rc_o)
+        return rc_o;
     if (per_sm < 1)
         return fail(RTC_ERR_CUDA, "path kernel does not fit on an SM (smem %zu)", smem);
     long long tasks = (long long)a.out_w * a.out_h * planes; // upper bound when a list is used
     long long want = (tasks + rtc::PATH_THREADS - 1) / rtc::PATH_THREADS;
     int blocks = (int)std::min<long long>((long long)sc->nsm * per_sm, want > 0 ? want : 1);
     int per_sm_g = 0;
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_g, kern_groups, rtc::PATH_THREADS, smem));
+    if ((rc_o = kernel_occupancy(sc->device, reinterpret_cast<const void *>(kern_groups), rtc::PATH_THREADS, smem, &per_sm_g)))
+        return rc_o;
     if (per_sm_g < 1)
         return fail(RTC_ERR_CUDA, "path kernel (group mode) does not fit on an SM (smem %zu)", smem);
     const int blocks_g = sc->nsm * std::min(per_sm_g, rtc::PATH_GROUP_CTAS);
@@ -737,8 +766,10 @@ static int render_device_impl(const RtcScene *sc, const Scene *sky, const Camera
             size_t bsmem = rtc::skyblock_smem_bytes(sc->ntris, sw.stream != 0);
             dim3 bgrid((job->out_w + 8 * rtc::BLK_W - 1) / (8 * rtc::BLK_W),
                        (job->out_h + 4 * rtc::BLK_H * rtc::SKYB_WARPS - 1) / (4 * rtc::BLK_H * rtc::SKYB_WARPS), planes);
-            CU(cudaFuncSetAttribute(rtc::render_skyblock_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)bsmem));
+            int sky_per_sm = 0;
+            if ((rc = kernel_occupancy(sc->device, reinterpret_cast<const void *>(rtc::render_skyblock_kernel),
+                                       rtc::SKYB_THREADS, bsmem, &sky_per_sm)))
+                return rc;
             if (msc->prog && job->nsplit <= 1 && d_rgb) {
                 a.prog = msc->prog;
                 a.prog_rows = msc->prog_rows;
@@ -769,10 +800,9 @@ static int render_device_impl(const RtcScene *sc, const Scene *sky, const Camera
                 tw.stream = sw.stream;
                 const size_t tsmem = rtc::sky_smem_bytes(sc->ntris, sw.stream != 0);
                 int per_sm = 0;
-                CU(cudaFuncSetAttribute(rtc::render_blocktask_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)tsmem));
-                CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rtc::render_blocktask_kernel,
-                                                                 rtc::BTASK_THREADS, tsmem));
+                if ((rc = kernel_occupancy(sc->device, reinterpret_cast<const void *>(rtc::render_blocktask_kernel),
+                                           rtc::BTASK_THREADS, tsmem, &per_sm)))
+                    return rc;
                 if (per_sm < 1)
                     return fail(RTC_ERR_CUDA, "block-task kernel does not fit on an SM");
                 const bool overlap = env_int("RTC_NO_OVERLAP", 0) == 0;
@@ -884,6 +914,7 @@ int rtc_quantize_device(int device, const float *d_accum, uint8_t *d_rgb, size_t
 // with ncclAllGather (NCCL is dlopen'ed so a 1-GPU caller has no NCCL
 // dependency), finish (un-interleave / ordered sum + quantise) and download.
 
+#include <chrono>
 #include <dlfcn.h>
 #include <nccl.h>
 
@@ -1075,6 +1106,10 @@ int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const
 {
     const int W = p->width, H = p->height;
     int G = p->ngpus > 1 ? p->ngpus : 1;
+    const bool trace = getenv("RTC_TRACE") != nullptr;
+    const auto t_entry = std::chrono::steady_clock::now();
+    auto since = [&]() { return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_entry).count(); };
+    double t_enq = 0, t_sync = 0;
     int ndev = rtc_device_count();
     if (ndev <= 0)
         return fail(RTC_ERR_NO_GPU, "no CUDA device: librtc_b200 has no CPU fallback");
@@ -1151,8 +1186,9 @@ int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const
             if ((rc = ensure(reinterpret_cast<void **>(&s.img), &s.img_bytes, img_bytes)))
                 return rc;
         // one GPU, plain frame: the device->host copy runs chunk by chunk on its own stream, behind the kernels
-        pipelined = G == 1 && S == 1 && !samples && H >= 8 * COPY_CHUNKS && wait_value32() != nullptr &&
-                    getenv("RTC_NO_PIPELINE") == nullptr;
+        // (only frames whose copy takes long enough to be worth 2 x COPY_CHUNKS more runtime calls)
+        pipelined = G == 1 && S == 1 && !samples && H >= 8 * COPY_CHUNKS && img_bytes >= (size_t)env_int("RTC_PIPELINE_MIN_BYTES", 4 << 20) &&
+                    wait_value32() != nullptr && getenv("RTC_NO_PIPELINE") == nullptr;
         if (pipelined) {
             if (!s.copy)
                 CU(cudaStreamCreateWithFlags(&s.copy, cudaStreamNonBlocking));
@@ -1234,6 +1270,7 @@ int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const
         CU(cudaMemcpyAsync(out_rgb, d_final, img_bytes, cudaMemcpyDeviceToHost, s0.stream));
     }
 
+    t_enq = since();
     // ids and counters
     std::vector<int32_t> tmp;
     unsigned long long tot[RTC_DEVICE_STATS_WORDS] = {0};
@@ -1245,6 +1282,7 @@ int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const
         CU(cudaStreamSynchronize(s.stream));
         if (pipelined)
             CU(cudaStreamSynchronize(s.copy));
+        t_sync = since();
         unsigned long long h[RTC_DEVICE_STATS_WORDS];
         CU(cudaMemcpy(h, s.stats, sizeof h, cudaMemcpyDeviceToHost));
         for (int i = 0; i < RTC_DEVICE_STATS_WORDS; ++i)
@@ -1289,6 +1327,9 @@ int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const
         int per_dev = 1 + (p->ntris > 0) + (p->nspheres > 0) + ((!samples && S > 1) ? 1 : 0);
         st->kernels_launched = per_dev * G + (G > 1 ? 1 : 0);
     }
+    if (trace)
+        fprintf(stderr, "rtc_b200: render_cuda host timeline: enqueued at %.0f us, synchronised at %.0f us, done at %.0f us\n",
+                t_enq, t_sync, since());
     return RTC_OK;
 }
 

@@ -128,6 +128,7 @@ def test_pipelined_copy_matches_plain_copy(height, monkeypatch):
     path = os.path.join(os.path.dirname(__file__), "golden", "scenes", "ultracomplex.tris")
     tris = np.fromfile(path, dtype=rtc.TRI_DTYPE)
     kw = dict(width=257, height=height, spp=5, max_bounce=3, triangles_only=1)
+    monkeypatch.setenv("RTC_PIPELINE_MIN_BYTES", "0")  # by default only frames of 4 MB and more are pipelined
     monkeypatch.setenv("RTC_NO_PIPELINE", "1")
     ref, _, st0 = rtc.render(tris, **kw)
     monkeypatch.delenv("RTC_NO_PIPELINE")
