@@ -60,7 +60,11 @@ static int load_mtl(const char *path, Mtl **out, int *count)
             char name[256];
             if (sscanf(line, "newmtl %255s", name) == 1 && cur + 1 < n) {
                 cur++;
-                strncpy(m[cur].name, name, sizeof m[cur].name - 1);
+                size_t nl = strlen(name);
+                if (nl > sizeof m[cur].name - 1)
+                    nl = sizeof m[cur].name - 1; /* the fixed-size field truncates long names */
+                memcpy(m[cur].name, name, nl);
+                m[cur].name[nl] = '\0';
             }
         }
         if (cur < 0)
