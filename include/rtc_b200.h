@@ -214,6 +214,12 @@ int rtc_uninterleave_device(int device, const void *d_parts, void *d_img, int el
  * The roofline denominator of the intersection kernel (MEASURED_PEAKS.json has no FP32 figure). */
 int rtc_fp32_peak_probe(int device, int reps, double *tflops, double *ms_best);
 
+/* Test probes (host buffers): the device versions of RandomDiretion (moremath.c:105-109; out = 3 floats per state,
+ * out_states = the RNG state after the 6 draws) and getEnvironmentLight (raytracing.c:151-160; dirs/out = 3 floats
+ * each) on n independent inputs, so that the FP64 islands can be compared with the reference at scale. */
+int rtc_probe_random_direction(int device, const uint32_t *states, int32_t n, float *out, uint32_t *out_states);
+int rtc_probe_environment_light(int device, const Scene *sky, const float *dirs, int32_t n, float *out);
+
 #ifdef __cplusplus
 }
 #endif

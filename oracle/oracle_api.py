@@ -246,6 +246,27 @@ class Oracle:
         self._fn("random_direction")(C.byref(s), o)
         return tuple(o), s.value
 
+    def random_direction_batch(self, states: np.ndarray):
+        """RandomDiretion on n independent states -> (float32 [n, 3], uint32 [n] states after)."""
+        st = np.ascontiguousarray(states, dtype=np.uint32)
+        out = np.empty((len(st), 3), dtype=np.float32)
+        after = np.empty(len(st), dtype=np.uint32)
+        f = self._fn("random_direction_batch")
+        f.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        f.restype = None
+        f(st.ctypes.data, len(st), out.ctypes.data, after.ctypes.data)
+        return out, after
+
+    def environment_light_batch(self, dirs: np.ndarray, scene) -> np.ndarray:
+        """getEnvironmentLight on n directions; `scene` is any ctypes struct with the reference Scene's layout."""
+        d = np.ascontiguousarray(dirs, dtype=np.float32).reshape(-1, 3)
+        out = np.empty_like(d)
+        f = self._fn("environment_light_batch")
+        f.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        f.restype = None
+        f(d.ctypes.data, len(d), C.addressof(scene), out.ctypes.data)
+        return out
+
     def environment_light(self, direction, scene: SceneC):
         p = (C.c_float * 3)(0, 0, 0)
         d = (C.c_float * 3)(*direction)

@@ -235,6 +235,16 @@ void ref_random_direction(uint32_t *state, float out[3])
     out[2] = v.z;
 }
 
+/* the same for n independent states (test probe at scale) */
+void ref_random_direction_batch(const uint32_t *states, int n, float *out, uint32_t *out_states)
+{
+    for (int i = 0; i < n; ++i) {
+        uint32_t st = states[i];
+        ref_random_direction(&st, out + 3 * (size_t)i);
+        out_states[i] = st;
+    }
+}
+
 void ref_environment_light(const float pos[3], const float dir[3], const OracleScene *s, float out[3])
 {
     Ray r = {{pos[0], pos[1], pos[2]}, {dir[0], dir[1], dir[2]}};
@@ -244,6 +254,14 @@ void ref_environment_light(const float pos[3], const float dir[3], const OracleS
     out[0] = v.x;
     out[1] = v.y;
     out[2] = v.z;
+}
+
+/* n directions at once (test probe at scale) */
+void ref_environment_light_batch(const float *dirs, int n, const OracleScene *s, float *out)
+{
+    const float pos[3] = {0.f, 0.f, 0.f};
+    for (int i = 0; i < n; ++i)
+        ref_environment_light(pos, dirs + 3 * (size_t)i, s, out + 3 * (size_t)i);
 }
 
 /* didHit/dst of one ray against triangle i / sphere k */

@@ -91,7 +91,8 @@ _lib = None
 EXPORTS = ["render_cuda", "render_cuda_shutdown", "rtc_camera_look_at", "rtc_normalize", "rtc_device_count",
            "rtc_last_error", "rtc_version", "rtc_scene_create", "rtc_scene_destroy", "rtc_subset_size",
            "rtc_render_device", "rtc_sum_quantize_device", "rtc_quantize_device", "rtc_render_launch_count",
-           "rtc_uninterleave_device", "rtc_fp32_peak_probe", "rtc_scene_update", "rtc_scene_kernel_times", "rtc_synth_scene"]
+           "rtc_uninterleave_device", "rtc_fp32_peak_probe", "rtc_scene_update", "rtc_scene_kernel_times", "rtc_synth_scene",
+           "rtc_probe_random_direction", "rtc_probe_environment_light"]
 
 
 def load_library() -> C.CDLL:
@@ -149,6 +150,10 @@ def load_library() -> C.CDLL:
     lib.rtc_synth_scene.restype = None
     lib.rtc_fp32_peak_probe.argtypes = [C.c_int, C.c_int, P(C.c_double), P(C.c_double)]
     lib.rtc_fp32_peak_probe.restype = C.c_int
+    lib.rtc_probe_random_direction.argtypes = [C.c_int, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
+    lib.rtc_probe_random_direction.restype = C.c_int
+    lib.rtc_probe_environment_light.argtypes = [C.c_int, P(Scene), C.c_void_p, C.c_int32, C.c_void_p]
+    lib.rtc_probe_environment_light.restype = C.c_int
     _lib = lib
     return lib
 
@@ -337,3 +342,21 @@ def fp32_peak_tflops(device: int = 0, reps: int = 5) -> float:
     t, ms = C.c_double(), C.c_double()
     _check(load_library().rtc_fp32_peak_probe(device, reps, C.byref(t), C.byref(ms)))
     return t.value
+
+
+def probe_random_direction(states: np.ndarray, device: int = 0):
+    """Device RandomDiretion on n independent RNG states -> (directions float32 [n, 3], states after uint32 [n])."""
+    st = np.ascontiguousarray(states, dtype=np.uint32)
+    out = np.empty((len(st), 3), dtype=np.float32)
+    after = np.empty(len(st), dtype=np.uint32)
+    _check(load_library().rtc_probe_random_direction(device, st.ctypes.data, len(st), out.ctypes.data, after.ctypes.data))
+    return out, after
+
+
+def probe_environment_light(dirs: np.ndarray, scene: Scene | None = None, device: int = 0) -> np.ndarray:
+    """Device getEnvironmentLight on n directions -> float32 [n, 3]."""
+    d = np.ascontiguousarray(dirs, dtype=np.float32).reshape(-1, 3)
+    sc = scene if scene is not None else make_scene()
+    out = np.empty_like(d)
+    _check(load_library().rtc_probe_environment_light(device, C.byref(sc), d.ctypes.data, len(d), out.ctypes.data))
+    return out

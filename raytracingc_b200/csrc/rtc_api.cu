@@ -371,6 +371,19 @@ int check_job(const RtcScene *sc, const Scene *sky, const Camera *cam, const Rtc
     return RTC_OK;
 }
 
+rtc::SkyParams make_sky(const Scene *sky)
+{
+    rtc::SkyParams k;
+    k.sun = to3(sky->normalizedSunDirection);
+    k.horizon = to3(sky->skyColorHorizon);
+    k.zenith = to3(sky->skyColorZenith);
+    k.ground = to3(sky->groundColor);
+    k.sunFocus = sky->sunFocus;
+    k.sunIntensity = sky->sunIntensity;
+    k.sun_skip_ok = (sky->sunFocus >= 0.0f && std::isfinite(sky->sunIntensity)) ? 1 : 0;
+    return k;
+}
+
 rtc::RenderArgs make_args(const RtcScene *sc, const Scene *sky, const Camera *cam, const RtcDeviceJob *job)
 {
     rtc::RenderArgs a;
@@ -379,13 +392,7 @@ rtc::RenderArgs make_args(const RtcScene *sc, const Scene *sky, const Camera *ca
     a.sc.ntris = sc->ntris;
     a.sc.s0 = sc->s0; a.sc.s1 = sc->s1; a.sc.s2 = sc->s2;
     a.sc.nsph = sc->nsph;
-    a.sky.sun = to3(sky->normalizedSunDirection);
-    a.sky.horizon = to3(sky->skyColorHorizon);
-    a.sky.zenith = to3(sky->skyColorZenith);
-    a.sky.ground = to3(sky->groundColor);
-    a.sky.sunFocus = sky->sunFocus;
-    a.sky.sunIntensity = sky->sunIntensity;
-    a.sky.sun_skip_ok = (sky->sunFocus >= 0.0f && std::isfinite(sky->sunIntensity)) ? 1 : 0;
+    a.sky = make_sky(sky);
     a.origin = to3(cam->origin);
     a.ex = to3(cam->ex);
     a.ey = to3(cam->ey);
@@ -1372,6 +1379,77 @@ __global__ void __launch_bounds__(256) ffma_probe_kernel(float *out, int iters, 
 } // namespace
 
 extern "C" {
+
+// ---- test probes: the device versions of two reference functions on arrays (host buffers) ----
+namespace {
+__global__ void probe_random_direction_kernel(const uint32_t *states, int n, float *out, uint32_t *out_states)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+        return;
+    const float4 r = rtc::random_direction(states[i]);
+    out[3 * (size_t)i] = r.x;
+    out[3 * (size_t)i + 1] = r.y;
+    out[3 * (size_t)i + 2] = r.z;
+    out_states[i] = __float_as_uint(r.w);
+}
+__global__ void probe_environment_light_kernel(const float *dirs, int n, rtc::SkyParams sky, float *out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+        return;
+    const rtc::f3 e = rtc::environment_light(rtc::mk3(dirs[3 * (size_t)i], dirs[3 * (size_t)i + 1], dirs[3 * (size_t)i + 2]), sky);
+    out[3 * (size_t)i] = e.x;
+    out[3 * (size_t)i + 1] = e.y;
+    out[3 * (size_t)i + 2] = e.z;
+}
+} // namespace
+
+int rtc_probe_random_direction(int device, const uint32_t *states, int32_t n, float *out, uint32_t *out_states)
+{
+    if (n < 0 || (n > 0 && (!states || !out || !out_states)))
+        return fail(RTC_ERR_ARG, "probe_random_direction: bad arguments");
+    if (rtc_device_count() <= device || device < 0)
+        return fail(RTC_ERR_NO_GPU, "probe_random_direction: device %d not visible", device);
+    if (n == 0)
+        return RTC_OK;
+    CU(cudaSetDevice(device));
+    uint32_t *d_s = nullptr, *d_os = nullptr;
+    float *d_o = nullptr;
+    CU(cudaMalloc(&d_s, sizeof(uint32_t) * (size_t)n));
+    CU(cudaMalloc(&d_os, sizeof(uint32_t) * (size_t)n));
+    CU(cudaMalloc(&d_o, sizeof(float) * 3 * (size_t)n));
+    CU(cudaMemcpy(d_s, states, sizeof(uint32_t) * (size_t)n, cudaMemcpyHostToDevice));
+    probe_random_direction_kernel<<<(n + 127) / 128, 128>>>(d_s, n, d_o, d_os);
+    CU(cudaGetLastError());
+    CU(cudaMemcpy(out, d_o, sizeof(float) * 3 * (size_t)n, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(out_states, d_os, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToHost));
+    cudaFree(d_s);
+    cudaFree(d_os);
+    cudaFree(d_o);
+    return RTC_OK;
+}
+
+int rtc_probe_environment_light(int device, const Scene *sky, const float *dirs, int32_t n, float *out)
+{
+    if (!sky || n < 0 || (n > 0 && (!dirs || !out)))
+        return fail(RTC_ERR_ARG, "probe_environment_light: bad arguments");
+    if (rtc_device_count() <= device || device < 0)
+        return fail(RTC_ERR_NO_GPU, "probe_environment_light: device %d not visible", device);
+    if (n == 0)
+        return RTC_OK;
+    CU(cudaSetDevice(device));
+    float *d_d = nullptr, *d_o = nullptr;
+    CU(cudaMalloc(&d_d, sizeof(float) * 3 * (size_t)n));
+    CU(cudaMalloc(&d_o, sizeof(float) * 3 * (size_t)n));
+    CU(cudaMemcpy(d_d, dirs, sizeof(float) * 3 * (size_t)n, cudaMemcpyHostToDevice));
+    probe_environment_light_kernel<<<(n + 127) / 128, 128>>>(d_d, n, make_sky(sky), d_o);
+    CU(cudaGetLastError());
+    CU(cudaMemcpy(out, d_o, sizeof(float) * 3 * (size_t)n, cudaMemcpyDeviceToHost));
+    cudaFree(d_d);
+    cudaFree(d_o);
+    return RTC_OK;
+}
 
 // Measured FP32 FFMA peak of `device` (MEASURED_PEAKS.json has no FP32 entry): best of `reps` launches.
 int rtc_fp32_peak_probe(int device, int reps, double *tflops, double *ms_best)
