@@ -561,6 +561,8 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
     w.write_ids = write_ids;
     w.coop = env_int("RTC_NO_COOP", 0) == 0;
     w.spec = env_int("RTC_NO_SPEC", 0) == 0;
+    w.spec_fails = env_int("RTC_SPEC_FAILS", 2);
+    w.spec_retry = env_int("RTC_SPEC_RETRY", 0);
     w.tile = env_int("RTC_PATH_TILE", rtc::PATH_TILE);
     if (w.tile < 1 || w.tile > rtc::PATH_TILE)
         w.tile = rtc::PATH_TILE;

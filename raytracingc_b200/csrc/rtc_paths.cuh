@@ -46,6 +46,8 @@ struct PathWork {
     int tile;                   // triangles per streamed tile (<= PATH_TILE), STREAM only
     int coop;                   // 1: cooperative sweep of the last live lanes (0 only for A/B measurements)
     unsigned group_lanes;       // lanes of the group-mode instantiation's grid (both instantiations decide with it)
+    int spec_fails;             // consecutive failed batches after which a pixel goes back to one sample at a time
+    int spec_retry;             // ... and the run of single-hit samples after which it tries batches again (0: never)
     int spec;                   // 1: group mode runs S consecutive samples of a pixel at once (see the kernel)
     const float4 *qrec;         // MODE >= 1: quick records (4 x float4 per triangle), built by quick_records_kernel
     float obound;               // MODE >= 1: the records are valid for ray origins with max |o_i| <= obound
@@ -617,8 +619,15 @@ __global__ void __launch_bounds__(PATH_THREADS, GROUPS ? PATH_GROUP_CTAS : RTC_P
                     bsample += nvalid;
                     if (nb > 1) {
                         fails = nvalid == 1 ? fails + 1 : 0;
-                        if (fails >= 2)
+                        if (fails >= w.spec_fails)
                             spec_on = false;
+                    } else if (!spec_on && w.spec_retry > 0) {
+                        // one sample at a time: samples that end at their first hit again re-arm the batches
+                        fails = dev ? 0 : fails - 1;
+                        if (fails <= -w.spec_retry) {
+                            spec_on = true;
+                            fails = w.spec_fails - 1;
+                        }
                     }
                     if (bsample >= s_end)
                         finish_pixel();
