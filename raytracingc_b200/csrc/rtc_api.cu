@@ -96,7 +96,8 @@ struct RtcScene {
     cudaEvent_t kev[3] = {nullptr, nullptr, nullptr}; // RTC_FLAG_TIME_KERNELS: before primary, between, after paths
     bool kev_valid = false;
     unsigned *counters = nullptr; // [0] list length, [1] path-kernel work cursor
-    float4 *qrec = nullptr;       // quick records of the path kernel's first phase (rtc_paths.cuh), 4 x float4 per triangle
+    float4 *qrec = nullptr;       // quick records of the path kernel's first phase (rtc_paths.cuh)
+    int q_layout = 0;             // layout qrec currently holds: 1 per triangle, 2 per pair (packed), 0 none
     int cap_q = 0;
     float q_obound = 0.f;         // origin bound the records were built for; 0 = not built for the current scene
     float bound_abs = 0.f;        // max |coordinate| over triangle vertices and sphere extents (host scan at upload)
@@ -526,8 +527,10 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
     rtc::PathWork w;
     // phase 1 of the sweep: quick records (1), + verification against the exact test (2), or the reference's arithmetic (0)
     const bool ref_quick = (flags & RTC_FLAG_REF_QUICK) != 0 || env_int("RTC_REF_QUICK", 0) != 0;
-    const int mode = ref_quick ? 0 : ((flags & RTC_FLAG_VERIFY_QUICK) ? 2 : (sc->quick_ok ? 1 : 0));
-    if (mode == 2 && !a.stats)
+    // quick records two triangles at a time with packed FP32 (modes 3, 4) unless RTC_QUICK_PACKED=0 (modes 1, 2)
+    const bool packed = env_int("RTC_QUICK_PACKED", 1) != 0;
+    const int mode = ref_quick ? 0 : ((flags & RTC_FLAG_VERIFY_QUICK) ? (packed ? 4 : 2) : (sc->quick_ok ? (packed ? 3 : 1) : 0));
+    if (rtc::mode_verify(mode) && !a.stats)
         return fail(RTC_ERR_ARG, "RTC_FLAG_VERIFY_QUICK needs a stats buffer");
     w.qrec = nullptr;
     w.obound = 0.f;
@@ -540,15 +543,19 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
         if (sc->ntris > sc->cap_q || !sc->qrec) {
             cudaFree(sc->qrec);
             sc->qrec = nullptr;
-            CU(cudaMalloc(&sc->qrec, sizeof(float4) * 4 * (size_t)(sc->ntris > 0 ? sc->ntris : 1)));
+            // room for either layout: 4 float4 per triangle, or QPAIR_F4 per pair of triangles
+            CU(cudaMalloc(&sc->qrec, sizeof(float4) * (rtc::path_q_f4(3, sc->ntris) + rtc::QPAIR_F4)));
             sc->cap_q = sc->ntris > 0 ? sc->ntris : 1;
             sc->q_obound = 0.f;
         }
-        if (!(need <= sc->q_obound) && sc->ntris > 0) {
-            const float ob = need * 1.25f;
-            rtc::quick_records_kernel<<<(sc->ntris + 127) / 128, 128, 0, st>>>(sc->geo, sc->ntris, ob, sc->qrec);
+        const int q_layout = rtc::mode_packed(mode) ? 2 : 1;
+        if ((!(need <= sc->q_obound) || sc->q_layout != q_layout) && sc->ntris > 0) {
+            const float ob = sc->q_layout != q_layout && need <= sc->q_obound ? sc->q_obound : need * 1.25f;
+            rtc::quick_records_kernel<<<(sc->ntris + 127) / 128, 128, 0, st>>>(sc->geo, sc->ntris, ob, sc->qrec,
+                                                                                 rtc::mode_packed(mode) ? 1 : 0);
             CU(cudaGetLastError());
             sc->q_obound = ob;
+            sc->q_layout = q_layout;
         }
         w.qrec = sc->qrec;
         w.obound = sc->q_obound;
@@ -566,17 +573,20 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
     w.tile = env_int("RTC_PATH_TILE", rtc::PATH_TILE);
     if (w.tile < 1 || w.tile > rtc::PATH_TILE)
         w.tile = rtc::PATH_TILE;
+    if (rtc::mode_packed(mode) && (w.tile & 1))
+        w.tile += 1; // pair records: a tile starts on an even triangle (PATH_TILE is even)
     const size_t resident = rtc::path_smem_bytes(sc->ntris, false, mode);
     const bool stream = env_int("RTC_FORCE_STREAM", 0) != 0 || resident > 96 * 1024;
     const size_t smem = rtc::path_smem_bytes(sc->ntris, stream, mode);
     int per_sm = 0;
     using PathKernel = void (*)(const rtc::RenderArgs, const rtc::PathWork);
     // [groups][stream][mode]: both group variants are launched, the device picks (see the kernel)
-    static const PathKernel kernels[2][2][3] = {
-        {{rtc::render_paths_kernel<false, 0, false>, rtc::render_paths_kernel<false, 1, false>, rtc::render_paths_kernel<false, 2, false>},
-         {rtc::render_paths_kernel<true, 0, false>, rtc::render_paths_kernel<true, 1, false>, rtc::render_paths_kernel<true, 2, false>}},
-        {{rtc::render_paths_kernel<false, 0, true>, rtc::render_paths_kernel<false, 1, true>, rtc::render_paths_kernel<false, 2, true>},
-         {rtc::render_paths_kernel<true, 0, true>, rtc::render_paths_kernel<true, 1, true>, rtc::render_paths_kernel<true, 2, true>}}};
+#define RTC_PATH_ROW(S_, G_)                                                                                       \
+    {rtc::render_paths_kernel<S_, 0, G_>, rtc::render_paths_kernel<S_, 1, G_>, rtc::render_paths_kernel<S_, 2, G_>, \
+     rtc::render_paths_kernel<S_, 3, G_>, rtc::render_paths_kernel<S_, 4, G_>}
+    static const PathKernel kernels[2][2][5] = {{RTC_PATH_ROW(false, false), RTC_PATH_ROW(true, false)},
+                                                {RTC_PATH_ROW(false, true), RTC_PATH_ROW(true, true)}};
+#undef RTC_PATH_ROW
     const PathKernel kern = kernels[0][stream ? 1 : 0][mode], kern_groups = kernels[1][stream ? 1 : 0][mode];
     int rc_o = kernel_occupancy(sc->device, reinterpret_cast<const void *>(kern), rtc::PATH_THREADS, smem, &per_sm);
     if (rc_o)

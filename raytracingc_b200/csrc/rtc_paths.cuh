@@ -56,13 +56,32 @@ struct PathWork {
                                 // kernel sweeps primary rays itself
 };
 
-// float4 per triangle in shared memory: geometry (3, what phase 2 reads) + in MODE 1, 2 the quick record (4, phase 1)
-__host__ __device__ constexpr int path_rec_f4(int mode) { return mode == 0 ? 3 : 7; }
+// MODE of the sweep's first phase: 0 the reference's arithmetic, 1 quick records, 2 = 1 + verification,
+// 3 quick records evaluated two triangles at a time with packed FP32 (FFMA2), 4 = 3 + verification.
+__host__ __device__ constexpr bool mode_packed(int mode) { return mode >= 3; }
+__host__ __device__ constexpr bool mode_verify(int mode) { return mode == 2 || mode == 4; }
 
+// Quick records of n triangles, in float4: 4 per triangle (MODE 1, 2), or 9 per PAIR of consecutive triangles
+// (MODE 3, 4): float4 j of a pair holds {slot 2j of the even triangle, slot 2j of the odd one, slot 2j+1 of the even
+// one, slot 2j+1 of the odd one} -- one LDS.128 gives two packed operands -- and the 9th float4 is padding: lanes
+// that read different pairs (cooperative sweep) are then 36 words apart and an LDS.128 of a quarter warp is free of
+// bank conflicts.  An odd count is completed by a record that drops every ray (thr = +inf).
+constexpr int QPAIR_F4 = 9;
+__host__ __device__ constexpr size_t path_q_f4(int mode, int n)
+{
+    return mode == 0 ? 0 : (mode_packed(mode) ? (size_t)QPAIR_F4 * (size_t)((n + 1) / 2) : (size_t)4 * (size_t)n);
+}
+// float index of slot s (0..15) of triangle i's record
+__host__ __device__ constexpr size_t path_q_slot(bool packed, int i, int s)
+{
+    return packed ? (size_t)(i >> 1) * (4 * QPAIR_F4) + (size_t)((s >> 1) * 4 + (s & 1) * 2 + (i & 1)) : (size_t)i * 16 + s;
+}
+
+// shared memory (per stage when streaming): [quick records of the stage's triangles][geometry, 3 float4 per triangle]
 __host__ __device__ inline size_t path_smem_bytes(int ntris, bool stream, int mode)
 {
-    const size_t rs = (size_t)path_rec_f4(mode) * sizeof(float4);
-    return stream ? (size_t)2 * PATH_TILE * rs : (size_t)(ntris > 0 ? ntris : 1) * rs;
+    const int n = stream ? PATH_TILE : (ntris > 0 ? ntris : 1);
+    return (stream ? 2 : 1) * (path_q_f4(mode, n) + (size_t)3 * n) * sizeof(float4);
 }
 
 // The reference's ray-triangle test arranged for SIMT, in two phases per chunk of 32 triangles.
@@ -150,7 +169,7 @@ __device__ __forceinline__ void tri_quick_bit(const f3 &o, const f3 &d, const fl
 constexpr float QUICK_DBOUND = 1.0625f;
 constexpr float QUICK_EPS = 0.0009999f; // just below the reference's 0.001f
 
-__global__ void quick_records_kernel(const float4 *__restrict__ geo, int n, float obound, float4 *__restrict__ q)
+__global__ void quick_records_kernel(const float4 *__restrict__ geo, int n, float obound, float4 *__restrict__ q, int packed)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n)
@@ -187,10 +206,20 @@ __global__ void quick_records_kernel(const float4 *__restrict__ geo, int n, floa
         thr = (X + M < (double)QUICK_EPS) ? (double)QUICK_EPS - M : -X;
     }
     const float fs = (float)f;
-    q[4 * i + 0] = make_float4(fs * g2.x, fs * g2.y, fs * g2.z, fs * (float)PU[0]);                   // AC~, PU~.x
-    q[4 * i + 1] = make_float4(fs * (float)PU[1], fs * (float)PU[2], -fs * g1.x, -fs * g1.y);         // PU~.yz, -AB~.xy
-    q[4 * i + 2] = make_float4(-fs * g1.z, -fs * (float)PV[0], -fs * (float)PV[1], -fs * (float)PV[2]); // -AB~.z, -PV~
-    q[4 * i + 3] = make_float4(fs * (float)N[0], fs * (float)N[1], fs * (float)N[2], __double2float_rd(thr));
+    // slots 0-2 AC~ (x m), 3-5 PU~ (x d), 6-8 -AB~ (x m), 9-11 -PV~ (x d), 12-14 N~ (x d), 15 thr
+    const float v[16] = {fs * g2.x,          fs * g2.y,          fs * g2.z,          fs * (float)PU[0],
+                         fs * (float)PU[1],  fs * (float)PU[2],  -fs * g1.x,         -fs * g1.y,
+                         -fs * g1.z,         -fs * (float)PV[0], -fs * (float)PV[1], -fs * (float)PV[2],
+                         fs * (float)N[0],   fs * (float)N[1],   fs * (float)N[2],   __double2float_rd(thr)};
+    float *qf = reinterpret_cast<float *>(q);
+#pragma unroll
+    for (int s = 0; s < 16; ++s)
+        qf[path_q_slot(packed != 0, i, s)] = v[s];
+    if (packed && i == n - 1 && (n & 1)) { // the pair's missing triangle: a record that drops every ray
+#pragma unroll
+        for (int s = 0; s < 16; ++s)
+            qf[path_q_slot(true, n, s)] = s == 15 ? __int_as_float(0x7f800000) : 0.f;
+    }
 }
 
 // the ray's side of the quick test: direction and moment
@@ -252,6 +281,147 @@ __device__ __forceinline__ void tri_quick2_bit(const QuickRay &r, const float4 &
         : "f"(v.U), "f"(nM), "f"(v.V), "f"(v.sum), "f"(v.hi), "f"(v.det), "f"(v.M), "f"(v.thr), "n"(BIT));
 }
 
+// ---- MODE 3: the same quick test, two consecutive triangles at a time with packed FP32 (sm_100a FFMA2 / FMUL2 /
+// FADD2: one issue slot for two FMAs).  Every half of a packed operation is the IEEE operation of the scalar code
+// above, in the same order, so the values -- and with them the margins' derivation -- are those of MODE 1 bit for
+// bit; only the issue count per pair changes (18 FMA-pipe slots -> 9).  The ray's scalars enter as the broadcast
+// operand (SASS Rx.F32), the two triangles' constants come interleaved from the pair record (path_q_slot).
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi)
+{
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpk2(f32x2 v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c)
+{
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b)
+{
+    f32x2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b)
+{
+    f32x2 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b)
+{
+    f32x2 r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+
+struct QuickRay2 { // the ray's six scalars, each in both halves
+    f32x2 dx, dy, dz, mx, my, mz;
+};
+__device__ __forceinline__ QuickRay2 quick_ray2(const QuickRay &r)
+{
+    QuickRay2 q;
+    q.dx = pk2(r.d.x, r.d.x);
+    q.dy = pk2(r.d.y, r.d.y);
+    q.dz = pk2(r.d.z, r.d.z);
+    q.mx = pk2(r.m.x, r.m.x);
+    q.my = pk2(r.m.y, r.m.y);
+    q.mz = pk2(r.m.z, r.m.z);
+    return q;
+}
+
+// quick values of the two triangles of pair record P (8 float4); v0 = even triangle, v1 = odd triangle
+__device__ __forceinline__ void quick_vals2(const QuickRay2 &r, const float4 *P, QuickVals &v0, QuickVals &v1)
+{
+    const ulonglong2 *Q = reinterpret_cast<const ulonglong2 *>(P);
+    const ulonglong2 q0 = Q[0], q1 = Q[1], q2 = Q[2], q3 = Q[3], q4 = Q[4], q5 = Q[5], q6 = Q[6], q7 = Q[7];
+    const f32x2 U = fma2(q2.y, r.dz, fma2(q2.x, r.dy, fma2(q1.y, r.dx, fma2(q1.x, r.mz, fma2(q0.y, r.my, mul2(q0.x, r.mx))))));
+    const f32x2 V = fma2(q5.y, r.dz, fma2(q5.x, r.dy, fma2(q4.y, r.dx, fma2(q4.x, r.mz, fma2(q3.y, r.my, mul2(q3.x, r.mx))))));
+    const f32x2 det = fma2(q7.x, r.dz, fma2(q6.y, r.dy, mul2(q6.x, r.dx)));
+    const f32x2 sum = add2(U, V);
+    const f32x2 M = sub2(pk2(QUICK_EPS, QUICK_EPS), q7.y);
+    const f32x2 hi = fma2(det, pk2(1.0000019073486328f, 1.0000019073486328f), M);
+    unpk2(U, v0.U, v1.U);
+    unpk2(V, v0.V, v1.V);
+    unpk2(det, v0.det, v1.det);
+    unpk2(sum, v0.sum, v1.sum);
+    unpk2(M, v0.M, v1.M);
+    unpk2(hi, v0.hi, v1.hi);
+    unpk2(q7.y, v0.thr, v1.thr);
+}
+
+// The same values for two pair records (four triangles), the FFMA2s ordered by RAY component: consecutive
+// instructions then share their broadcast operand (operand-reuse cache), so each reads only the triangles' pair and
+// the accumulator from the register file -- FFMA2 with three fresh 64-bit operands is bound by the register ports
+// (tools/pipe_probe.cu: 1.26 FFMA2/clk/SM against 3.6 FFMA/clk/SM).
+__device__ __forceinline__ void quick_vals2x2(const QuickRay2 &r, const float4 *P, QuickVals (&v)[4])
+{
+    const ulonglong2 *Qa = reinterpret_cast<const ulonglong2 *>(P), *Qb = reinterpret_cast<const ulonglong2 *>(P + QPAIR_F4);
+    f32x2 Ua = mul2(Qa[0].x, r.mx), Ub = mul2(Qb[0].x, r.mx), Va = mul2(Qa[3].x, r.mx), Vb = mul2(Qb[3].x, r.mx);
+    Ua = fma2(Qa[0].y, r.my, Ua), Ub = fma2(Qb[0].y, r.my, Ub), Va = fma2(Qa[3].y, r.my, Va), Vb = fma2(Qb[3].y, r.my, Vb);
+    Ua = fma2(Qa[1].x, r.mz, Ua), Ub = fma2(Qb[1].x, r.mz, Ub), Va = fma2(Qa[4].x, r.mz, Va), Vb = fma2(Qb[4].x, r.mz, Vb);
+    f32x2 Da = mul2(Qa[6].x, r.dx), Db = mul2(Qb[6].x, r.dx);
+    Ua = fma2(Qa[1].y, r.dx, Ua), Ub = fma2(Qb[1].y, r.dx, Ub), Va = fma2(Qa[4].y, r.dx, Va), Vb = fma2(Qb[4].y, r.dx, Vb);
+    Da = fma2(Qa[6].y, r.dy, Da), Db = fma2(Qb[6].y, r.dy, Db);
+    Ua = fma2(Qa[2].x, r.dy, Ua), Ub = fma2(Qb[2].x, r.dy, Ub), Va = fma2(Qa[5].x, r.dy, Va), Vb = fma2(Qb[5].x, r.dy, Vb);
+    Da = fma2(Qa[7].x, r.dz, Da), Db = fma2(Qb[7].x, r.dz, Db);
+    Ua = fma2(Qa[2].y, r.dz, Ua), Ub = fma2(Qb[2].y, r.dz, Ub), Va = fma2(Qa[5].y, r.dz, Va), Vb = fma2(Qb[5].y, r.dz, Vb);
+    const f32x2 eps = pk2(QUICK_EPS, QUICK_EPS), k = pk2(1.0000019073486328f, 1.0000019073486328f);
+    const f32x2 ta = Qa[7].y, tb = Qb[7].y;
+    const f32x2 Ma = sub2(eps, ta), Mb = sub2(eps, tb);
+    const f32x2 Sa = add2(Ua, Va), Sb = add2(Ub, Vb);
+    const f32x2 Ha = fma2(Da, k, Ma), Hb = fma2(Db, k, Mb);
+    unpk2(Ua, v[0].U, v[1].U), unpk2(Ub, v[2].U, v[3].U);
+    unpk2(Va, v[0].V, v[1].V), unpk2(Vb, v[2].V, v[3].V);
+    unpk2(Da, v[0].det, v[1].det), unpk2(Db, v[2].det, v[3].det);
+    unpk2(Sa, v[0].sum, v[1].sum), unpk2(Sb, v[2].sum, v[3].sum);
+    unpk2(Ma, v[0].M, v[1].M), unpk2(Mb, v[2].M, v[3].M);
+    unpk2(Ha, v[0].hi, v[1].hi), unpk2(Hb, v[2].hi, v[3].hi);
+    unpk2(ta, v[0].thr, v[1].thr), unpk2(tb, v[2].thr, v[3].thr);
+}
+
+__device__ __forceinline__ bool quick_keep(const QuickVals &v)
+{
+    bool p = !(v.U < -v.M);
+    p = p && !(v.V < -v.M);
+    p = p && !(v.sum > v.hi);
+    p = p || !(v.det > v.M);
+    p = p && !(v.det < v.thr);
+    return p;
+}
+
+template <unsigned BIT>
+__device__ __forceinline__ void quick_keep_bit(const QuickVals &v, unsigned &m)
+{
+    const float nM = -v.M;
+    asm("{\n\t.reg .pred p;\n\t"
+        "setp.geu.f32 p, %1, %2;\n\t"        // !(U < -M)
+        "setp.geu.and.f32 p, %3, %2, p;\n\t" // !(V < -M)
+        "setp.leu.and.f32 p, %4, %5, p;\n\t" // !(U + V > hi)
+        "setp.leu.or.f32 p, %6, %7, p;\n\t"  // or the sign of det is not known: !(det > M)
+        "setp.geu.and.f32 p, %6, %8, p;\n\t" // !(det < thr)
+        "@p or.b32 %0, %0, %9;\n\t}"
+        : "+r"(m)
+        : "f"(v.U), "f"(nM), "f"(v.V), "f"(v.sum), "f"(v.hi), "f"(v.det), "f"(v.M), "f"(v.thr), "n"(BIT));
+}
+
+// K-th .. (N-1)-th PAIR of a group of N consecutive pair records: bits 2K, 2K+1 of mg
+template <int K, int N>
+__device__ __forceinline__ void quick2_pairs(const QuickRay2 &r, const float4 *P, unsigned &mg)
+{
+    if constexpr (K < N) {
+        QuickVals v0, v1;
+        quick_vals2(r, P + QPAIR_F4 * K, v0, v1);
+        quick_keep_bit<(1u << (2 * K))>(v0, mg);
+        quick_keep_bit<(2u << (2 * K))>(v1, mg);
+        quick2_pairs<K + 1, N>(r, P, mg);
+    }
+}
+
 // K-th .. (N-1)-th pair of a group of N consecutive records: bit K of mg
 template <int K, int N>
 __device__ __forceinline__ void quick2_group(const QuickRay &r, const float4 *R, unsigned &mg)
@@ -272,7 +442,8 @@ __device__ __forceinline__ bool quick_ray_ok(const f3 &o, const f3 &d, float obo
 
 // MODE 0: S = geo = geometry tile (3 float4 per triangle), quick test in the reference's arithmetic.
 // MODE 1: S = quick-record tile (4 float4 per triangle), geo = geometry tile of the same triangles (phase 2).
-// MODE 2: MODE 1 + every pair also runs the exact test; an accepted pair the quick test dropped is counted (viol).
+// MODE 3: S = pair-record tile (QPAIR_F4 float4 per two triangles), packed quick test.
+// MODE 2, 4: MODE 1, 3 + every pair also runs the exact test; an accepted pair the quick test dropped is counted (viol).
 template <int MODE>
 __device__ __forceinline__ void sweep_chunked(const float4 *S, const float4 *geo, float obound, int n, int base,
                                               bool active, const f3 &o, const f3 &d, float &best, int &bestId,
@@ -280,6 +451,7 @@ __device__ __forceinline__ void sweep_chunked(const float4 *S, const float4 *geo
 {
     const bool rayok = MODE == 0 || quick_ray_ok(o, d, obound);
     const QuickRay qr = quick_ray(o, d);
+    const QuickRay2 qr2 = quick_ray2(qr);
     for (int c0 = 0; c0 < n; c0 += 32) {
         const int cn = min(32, n - c0);
         unsigned m = 0;
@@ -302,6 +474,25 @@ __device__ __forceinline__ void sweep_chunked(const float4 *S, const float4 *geo
                     tri_quick_bit<1u>(o, d, S[3 * (c0 + j)], S[3 * (c0 + j) + 1], S[3 * (c0 + j) + 2], m1);
                     m |= m1 << j;
                 }
+            } else if (mode_packed(MODE)) {
+                constexpr int UP = RTC_QUICK_UNROLL >= 2 ? RTC_QUICK_UNROLL / 2 : 1; // pairs per iteration
+                const float4 *P = S + QPAIR_F4 * (c0 >> 1);
+                const int np = (cn + 1) >> 1;
+                int j = 0;
+#pragma unroll 1
+                for (; j + UP <= np; j += UP) {
+                    unsigned mg = 0;
+                    quick2_pairs<0, UP>(qr2, P + QPAIR_F4 * j, mg);
+                    m |= mg << (2 * j);
+                }
+#pragma unroll 1
+                for (; j < np; ++j) {
+                    unsigned m1 = 0;
+                    quick2_pairs<0, 1>(qr2, P + QPAIR_F4 * j, m1);
+                    m |= m1 << (2 * j);
+                }
+                if (cn < 32)
+                    m &= (1u << cn) - 1u; // an odd count's last pair is completed by a record that never survives
             } else {
                 constexpr int UN = RTC_QUICK_UNROLL;
                 int j = 0;
@@ -317,7 +508,7 @@ __device__ __forceinline__ void sweep_chunked(const float4 *S, const float4 *geo
                 }
             }
         }
-        if (MODE == 2 && active) {
+        if (mode_verify(MODE) && active) {
             for (int j = 0; j < cn; ++j) {
                 const int i = c0 + j;
                 unsigned ex[6] = {0, 0, 0, 0, 0, 0};
@@ -367,6 +558,23 @@ __device__ __forceinline__ void coop_tile(CoopCtx &c, const float4 *S_, const fl
         for (int j = c.r; j < n; j += c.S)
             if (tri_quick(c.o, c.d, S_[3 * j], S_[3 * j + 1], S_[3 * j + 2]))
                 tri_test_exact<false>(c.o, c.d, S_[3 * j], S_[3 * j + 1], S_[3 * j + 2], base + j, c.best, c.id, dummy);
+    } else if (mode_packed(MODE)) { // member r takes the pairs r, r + S, ...
+        const bool rayok = quick_ray_ok(c.o, c.d, obound);
+        const QuickRay2 qr2 = quick_ray2(quick_ray(c.o, c.d));
+        for (int q = c.r; 2 * q < n; q += c.S) {
+            bool k0 = true, k1 = true;
+            if (rayok) {
+                QuickVals v0, v1;
+                quick_vals2(qr2, S_ + QPAIR_F4 * q, v0, v1);
+                k0 = quick_keep(v0);
+                k1 = quick_keep(v1);
+            }
+            const int j = 2 * q;
+            if (k0)
+                tri_test_exact<false>(c.o, c.d, geo[3 * j], geo[3 * j + 1], geo[3 * j + 2], base + j, c.best, c.id, dummy);
+            if (k1 && j + 1 < n)
+                tri_test_exact<false>(c.o, c.d, geo[3 * j + 3], geo[3 * j + 4], geo[3 * j + 5], base + j + 1, c.best, c.id, dummy);
+        }
     } else {
         const bool rayok = quick_ray_ok(c.o, c.d, obound);
         const QuickRay qr = quick_ray(c.o, c.d);
@@ -382,7 +590,7 @@ __device__ __forceinline__ void coop_tile(CoopCtx &c, const float4 *S_, const fl
 // (the group instantiation is capped at the registers of PATH_GROUP_CTAS CTAs per SM and launched with exactly that
 // grid: its S is chosen for a fully resident grid)
 template <bool STREAM, int MODE, bool GROUPS>
-__global__ void __launch_bounds__(PATH_THREADS, GROUPS ? PATH_GROUP_CTAS : RTC_PATH_MINB) render_paths_kernel(const RenderArgs a, const PathWork w)
+__global__ void __launch_bounds__(PATH_THREADS, GROUPS ? PATH_GROUP_CTAS : ((MODE == 3 && !STREAM) ? 6 : RTC_PATH_MINB)) render_paths_kernel(const RenderArgs a, const PathWork w)
 {
     {
         const unsigned np = w.list ? *w.list_count : (unsigned)(a.out_w * a.out_h);
@@ -391,9 +599,10 @@ __global__ void __launch_bounds__(PATH_THREADS, GROUPS ? PATH_GROUP_CTAS : RTC_P
             return;
     }
     extern __shared__ float4 sGeo[];
-    // shared memory (per stage when streaming): [quick records, 4 float4 per triangle (MODE >= 1)][geometry, 3 per triangle]
-    constexpr int RS = path_rec_f4(MODE), QS = RS - 3;
-    const int cap = STREAM ? PATH_TILE : a.sc.ntris; // triangles a stage holds
+    // shared memory (per stage when streaming): [quick records (MODE >= 1), path_q_f4][geometry, 3 float4 per triangle]
+    const int cap = STREAM ? PATH_TILE : a.sc.ntris;       // triangles a stage holds
+    const int qoff = (int)path_q_f4(MODE, cap);             // float4 offset of the stage's geometry
+    constexpr int STAGE_F4 = (int)path_q_f4(MODE, PATH_TILE) + 3 * PATH_TILE;
     __shared__ uint64_t bars[2];
     const int ntris = a.sc.ntris;
     const int nsph = a.trianglesOnly ? 0 : a.sc.nsph;
@@ -402,10 +611,10 @@ __global__ void __launch_bounds__(PATH_THREADS, GROUPS ? PATH_GROUP_CTAS : RTC_P
     const int ntiles = STREAM ? (ntris + tile - 1) / tile : 1;
 
     if (!STREAM) {
-        for (int i = threadIdx.x; i < QS * ntris; i += PATH_THREADS)
+        for (int i = threadIdx.x; i < qoff; i += PATH_THREADS)
             sGeo[i] = w.qrec[i];
         for (int i = threadIdx.x; i < 3 * ntris; i += PATH_THREADS)
-            sGeo[QS * cap + i] = a.sc.geo[i];
+            sGeo[qoff + i] = a.sc.geo[i];
     } else if (threadIdx.x == 0) {
         mbar_init(&bars[0], 1);
         mbar_init(&bars[1], 1);
@@ -461,18 +670,19 @@ __global__ void __launch_bounds__(PATH_THREADS, GROUPS ? PATH_GROUP_CTAS : RTC_P
     int id0 = -1, bestId = -1;
     bool pend = false; // (best, bestId) of the last sweep is a hit that is not shaded yet
     unsigned long long nrays = 0, nhitpix = 0;
-    unsigned viol = 0; // MODE 2: accepted pairs the quick test dropped (must stay 0)
+    unsigned viol = 0; // MODE 2, 4: accepted pairs the quick test dropped (must stay 0)
     uint32_t k0 = 0; // tiles consumed so far (STREAM): stage = k & 1, parity = (k >> 1) & 1
 
     auto issue = [&](uint32_t k, int t) {
         const int n = min(tile, ntris - t * tile);
-        const uint32_t bq = (uint32_t)n * (uint32_t)QS * (uint32_t)sizeof(float4), bg = (uint32_t)n * 3u * (uint32_t)sizeof(float4);
-        float4 *stage = sGeo + (size_t)(k & 1) * PATH_TILE * RS;
+        // (packed records: the host keeps the tile even, so a tile starts on a pair)
+        const uint32_t bq = (uint32_t)path_q_f4(MODE, n) * (uint32_t)sizeof(float4), bg = (uint32_t)n * 3u * (uint32_t)sizeof(float4);
+        float4 *stage = sGeo + (size_t)(k & 1) * STAGE_F4;
         fence_proxy_async();
         mbar_arrive_expect_tx(&bars[k & 1], bq + bg);
-        if (QS)
-            tma_load_1d(stage, w.qrec + (size_t)t * tile * QS, bq, &bars[k & 1]);
-        tma_load_1d(stage + QS * PATH_TILE, a.sc.geo + (size_t)t * tile * 3, bg, &bars[k & 1]);
+        if (MODE != 0)
+            tma_load_1d(stage, w.qrec + path_q_f4(MODE, t * tile), bq, &bars[k & 1]);
+        tma_load_1d(stage + qoff, a.sc.geo + (size_t)t * tile * 3, bg, &bars[k & 1]);
     };
 
     // the pixel's last sample is accumulated: write it
@@ -716,10 +926,10 @@ __global__ void __launch_bounds__(PATH_THREADS, GROUPS ? PATH_GROUP_CTAS : RTC_P
         }
         if (!STREAM) {
             if (coop || grouped) {
-                coop_tile<MODE>(cc, sGeo, sGeo + QS * cap, w.obound, ntris, 0);
+                coop_tile<MODE>(cc, sGeo, sGeo + qoff, w.obound, ntris, 0);
                 coop_finish();
             } else {
-                sweep_chunked<MODE>(sGeo, sGeo + QS * cap, w.obound, ntris, 0, sweeping, L.pos, L.dir, best, bestId, viol);
+                sweep_chunked<MODE>(sGeo, sGeo + qoff, w.obound, ntris, 0, sweeping, L.pos, L.dir, best, bestId, viol);
             }
         } else {
             if (threadIdx.x == 0) {
@@ -730,11 +940,11 @@ __global__ void __launch_bounds__(PATH_THREADS, GROUPS ? PATH_GROUP_CTAS : RTC_P
             for (int t = 0; t < ntiles; ++t) {
                 const uint32_t k = k0 + (uint32_t)t;
                 mbar_wait(&bars[k & 1], (k >> 1) & 1u);
-                const float4 *stage = sGeo + (size_t)(k & 1) * PATH_TILE * RS;
+                const float4 *stage = sGeo + (size_t)(k & 1) * STAGE_F4;
                 if (coop || grouped)
-                    coop_tile<MODE>(cc, stage, stage + QS * PATH_TILE, w.obound, min(tile, ntris - t * tile), t * tile);
+                    coop_tile<MODE>(cc, stage, stage + qoff, w.obound, min(tile, ntris - t * tile), t * tile);
                 else
-                    sweep_chunked<MODE>(stage, stage + QS * PATH_TILE, w.obound, min(tile, ntris - t * tile), t * tile,
+                    sweep_chunked<MODE>(stage, stage + qoff, w.obound, min(tile, ntris - t * tile), t * tile,
                                         sweeping, L.pos, L.dir, best, bestId, viol);
                 __syncthreads(); // every warp is done with this stage
                 if (threadIdx.x == 0 && t + 2 < ntiles)
@@ -776,7 +986,7 @@ __global__ void __launch_bounds__(PATH_THREADS, GROUPS ? PATH_GROUP_CTAS : RTC_P
             r += __shfl_xor_sync(0xffffffffu, r, o);
             hp += __shfl_xor_sync(0xffffffffu, hp, o);
         }
-        if (MODE == 2 && viol)
+        if (mode_verify(MODE) && viol)
             atomicAdd(&a.stats[ST_MISMATCH], (unsigned long long)viol);
         if (lane == 0 && r) {
             atomicAdd(&a.stats[ST_RAYS], r);

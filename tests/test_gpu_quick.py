@@ -10,6 +10,13 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True, params=["packed", "scalar"])
+def quick_layout(request, monkeypatch):
+    """Both evaluations of the quick records: two triangles at a time with packed FP32 (default), one at a time."""
+    monkeypatch.setenv("RTC_QUICK_PACKED", "1" if request.param == "packed" else "0")
+    return request.param
+
+
 def make_scene(rng, n, extent, size, normals="exact", offset=(0.0, 0.0, 6.0)):
     import raytracingc_b200 as rtc
     t = np.zeros(n, dtype=rtc.TRI_DTYPE)
@@ -52,6 +59,8 @@ SCENES = [
     ("slivers", 400, 4.0, 2e-2, "exact", (0, 0, 6)),        # dets around EPS
     ("tiny", 400, 3.0, 1e-3, "rounded", (0, 0, 6)),         # everything below EPS
     ("dense", 1500, 2.0, 0.5, "exact", (0, 0, 5)),          # many hits per ray, long bounce chains
+    ("odd", 333, 5.0, 1.5, "mixed", (0, 0, 6)),             # odd count: the last pair record is completed by a pad
+    ("one", 1, 0.5, 3.0, "exact", (0, 0, 6)),
 ]
 
 

@@ -44,6 +44,16 @@ def test_streamed_tiles_bit_identical(small_tiles, name):
     _render_and_check(name)
 
 
+@pytest.mark.parametrize("name", NAMES[:3])
+@pytest.mark.parametrize("packed,tile", [("0", "24"), ("0", "23"), ("1", "23"), ("1", "2")])
+def test_streamed_tiles_record_layouts(small_tiles, monkeypatch, name, packed, tile):
+    """Both quick-record layouts (per triangle / per pair for the packed FP32 evaluation) through the TMA tiles;
+    an odd tile request is rounded up to a whole pair in the packed layout."""
+    monkeypatch.setenv("RTC_QUICK_PACKED", packed)
+    monkeypatch.setenv("RTC_PATH_TILE", tile)
+    _render_and_check(name)
+
+
 @pytest.mark.parametrize("name", NAMES[:4])
 def test_paths_only_mode(name):
     from raytracingc_b200 import api

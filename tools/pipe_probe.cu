@@ -14,11 +14,13 @@ __global__ void __launch_bounds__(256) probe(float *out, float a, float b, int n
     float r[NCH];
     unsigned u[NCH];
     __half2 h[NCH], hs = __floats2half2_rn(a, b);
+    unsigned long long p2[NCH];
 #pragma unroll
     for (int k = 0; k < NCH; ++k) {
         r[k] = threadIdx.x + k;
         u[k] = threadIdx.x * 977u + k;
         h[k] = __floats2half2_rn(0.001f * threadIdx.x, 0.5f * k);
+        asm("mov.b64 %0, {%1, %2};" : "=l"(p2[k]) : "f"(0.5f + 1e-3f * k), "f"(0.25f + 1e-3f * threadIdx.x));
     }
     for (int i = 0; i < n; ++i) {
 #pragma unroll
@@ -45,12 +47,33 @@ __global__ void __launch_bounds__(256) probe(float *out, float a, float b, int n
             }
             if (MODE == 9) u[k] = max(u[k], u[(k + 1) % NCH]);            // IMNMX / VIMNMX (alu)
             if (MODE == 10) r[k] = fmaxf(r[k], r[(k + 1) % NCH]);         // FMNMX (alu)
+            if (MODE == 11) asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(p2[k]) : "l"(p2[(k + 1) % NCH]), "l"(p2[(k + 2) % NCH])); // FFMA2 3-reg
+            if (MODE == 12) {                                             // FFMA2 + FMNMX alternating (fma pipe + alu pipe)
+                asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(p2[k]) : "l"(p2[(k + 1) % NCH]), "l"(p2[(k + 2) % NCH]));
+                r[k] = fmaxf(r[k], r[(k + 1) % NCH]);
+            }
+            if (MODE == 13) {                                             // FFMA + FMNMX alternating
+                r[k] = fmaf(r[k], r[(k + 1) % NCH], r[(k + 2) % NCH]);
+                u[k] = max(u[k], u[(k + 1) % NCH]);
+            }
+            if (MODE == 14) {                                             // FFMA2 + FFMA alternating (same pipe?)
+                asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(p2[k]) : "l"(p2[(k + 1) % NCH]), "l"(p2[(k + 2) % NCH]));
+                r[k] = fmaf(r[k], r[(k + 1) % NCH], r[(k + 2) % NCH]);
+            }
+            if (MODE == 15) {                                             // 2 FFMA2 + 1 FSETP-like (packed sweep's mix)
+                asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(p2[k]) : "l"(p2[(k + 1) % NCH]), "l"(p2[(k + 2) % NCH]));
+                if ((k & 1) == 0) asm volatile("{.reg .pred q; setp.geu.f32 q, %1, %2; @q or.b32 %0, %0, 1;}" : "+r"(u[k]) : "f"(r[k]), "f"(r[(k + 1) % NCH]));
+            }
+            if (MODE == 16) {                                             // 2 FFMA + 1 FSETP-like (scalar sweep's mix)
+                r[k] = fmaf(r[k], a, b);
+                if ((k & 1) == 0) asm volatile("{.reg .pred q; setp.geu.f32 q, %1, %2; @q or.b32 %0, %0, 1;}" : "+r"(u[k]) : "f"(r[k]), "f"(r[(k + 1) % NCH]));
+            }
         }
     }
     float s = 0;
 #pragma unroll
     for (int k = 0; k < NCH; ++k)
-        s += r[k] + (float)u[k] + __low2float(h[k]) + __high2float(h[k]);
+        s += r[k] + (float)u[k] + __low2float(h[k]) + __high2float(h[k]) + (float)(p2[k] >> 13);
     if (s == 123.456f)
         out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
@@ -96,6 +119,12 @@ int main()
     run<3>("LOP3", NCH);
     run<9>("IMNMX", NCH);
     run<10>("FMNMX", NCH);
+    run<11>("FFMA2 r,r,r (warp-inst; x2 FMA each)", NCH);
+    run<12>("FFMA2 + FMNMX alternating", 2 * NCH);
+    run<13>("FFMA + IMNMX alternating", 2 * NCH);
+    run<14>("FFMA2 + FFMA alternating", 2 * NCH);
+    run<15>("2 FFMA2 + (FSETP + @p LOP)", NCH + NCH);
+    run<16>("2 FFMA + (FSETP + @p LOP)", NCH + NCH);
     run<4>("4 FADD + 2 LOP3 (x2)", NCH + NCH / 2);
     run<5>("2 HADD2 + 1 LOP3 (x4)", NCH + NCH / 2);
     return 0;

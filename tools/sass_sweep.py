@@ -28,7 +28,7 @@ for i, l in enumerate(lines):
     if m and int(m.group(1), 16) < addr(l):
         n = (addr(l) - int(m.group(1), 16)) // 16 + 1
         body = lines[i - n + 1:i + 1]
-        fp = sum(bool(re.search(r"\b(FMUL|FADD|FFMA)\b", b)) for b in body)
+        fp = sum(bool(re.search(r"\b(FMUL2?|FADD2?|FFMA2?)\b", b)) for b in body)
         if n < 400 and not any(re.search(r"\b(CALL|BSSY|LDG)\b", b) for b in body) and (best is None or fp > best[0]):
             best = (fp, body)
 body = best[1]
