@@ -528,8 +528,12 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
     // phase 1 of the sweep: quick records (1), + verification against the exact test (2), or the reference's arithmetic (0)
     const bool ref_quick = (flags & RTC_FLAG_REF_QUICK) != 0 || env_int("RTC_REF_QUICK", 0) != 0;
     // quick records two triangles at a time with packed FP32 (modes 3, 4) unless RTC_QUICK_PACKED=0 (modes 1, 2)
-    const bool packed = env_int("RTC_QUICK_PACKED", 1) != 0;
-    const int mode = ref_quick ? 0 : ((flags & RTC_FLAG_VERIFY_QUICK) ? (packed ? 4 : 2) : (sc->quick_ok ? (packed ? 3 : 1) : 0));
+    // RTC_QUICK_FORM: 1 one triangle at a time (modes 1, 2), 3 two triangles at a time with packed FP32 (3, 4; default).
+    // (RTC_QUICK_PACKED=0 is another spelling of form 1.)
+    int form = env_int("RTC_QUICK_FORM", env_int("RTC_QUICK_PACKED", 1) != 0 ? 3 : 1);
+    if (form != 1 && form != 3)
+        form = 3;
+    const int mode = ref_quick ? 0 : ((flags & RTC_FLAG_VERIFY_QUICK) ? form + 1 : (sc->quick_ok ? form : 0));
     if (rtc::mode_verify(mode) && !a.stats)
         return fail(RTC_ERR_ARG, "RTC_FLAG_VERIFY_QUICK needs a stats buffer");
     w.qrec = nullptr;
@@ -544,15 +548,14 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
             cudaFree(sc->qrec);
             sc->qrec = nullptr;
             // room for either layout: 4 float4 per triangle, or QPAIR_F4 per pair of triangles
-            CU(cudaMalloc(&sc->qrec, sizeof(float4) * (rtc::path_q_f4(3, sc->ntris) + rtc::QPAIR_F4)));
+            CU(cudaMalloc(&sc->qrec, sizeof(float4) * (rtc::path_q_f4(5, sc->ntris) + rtc::QPAIR_F4)));
             sc->cap_q = sc->ntris > 0 ? sc->ntris : 1;
             sc->q_obound = 0.f;
         }
-        const int q_layout = rtc::mode_packed(mode) ? 2 : 1;
+        const int q_layout = rtc::mode_layout(mode);
         if ((!(need <= sc->q_obound) || sc->q_layout != q_layout) && sc->ntris > 0) {
             const float ob = sc->q_layout != q_layout && need <= sc->q_obound ? sc->q_obound : need * 1.25f;
-            rtc::quick_records_kernel<<<(sc->ntris + 127) / 128, 128, 0, st>>>(sc->geo, sc->ntris, ob, sc->qrec,
-                                                                                 rtc::mode_packed(mode) ? 1 : 0);
+            rtc::quick_records_kernel<<<(sc->ntris + 127) / 128, 128, 0, st>>>(sc->geo, sc->ntris, ob, sc->qrec, q_layout);
             CU(cudaGetLastError());
             sc->q_obound = ob;
             sc->q_layout = q_layout;

@@ -28,12 +28,15 @@ namespace rtc {
 constexpr int PATH_THREADS = 128;
 constexpr int PATH_GROUP_CTAS = 5; // CTAs per SM of the group-mode instantiation
 #ifndef RTC_QUICK_UNROLL
-#define RTC_QUICK_UNROLL 4 // pairs per iteration of the branch-free first phase; A/B knob
+#define RTC_QUICK_UNROLL 8 // (ray, triangle) pairs per lane and iteration of the branch-free first phase; A/B knob (4: +1 %)
 #endif
 #ifdef RTC_PATH_MINBLOCKS // min resident CTAs per SM asked of the compiler (register cap); A/B knob
 #define RTC_PATH_MINB RTC_PATH_MINBLOCKS
 #else
 #define RTC_PATH_MINB 0
+#endif
+#ifndef RTC_PATH_MINB3 // ... of the resident packed-quick-test instantiation: 6 CTAs/SM = 80 registers (84 uncapped)
+#define RTC_PATH_MINB3 6
 #endif
 constexpr int PATH_TILE = 128; // triangles per streamed tile: 14 KB per stage (quick records + geometry), 2 stages
 
@@ -58,8 +61,12 @@ struct PathWork {
 
 // MODE of the sweep's first phase: 0 the reference's arithmetic, 1 quick records, 2 = 1 + verification,
 // 3 quick records evaluated two triangles at a time with packed FP32 (FFMA2), 4 = 3 + verification.
-__host__ __device__ constexpr bool mode_packed(int mode) { return mode >= 3; }
-__host__ __device__ constexpr bool mode_verify(int mode) { return mode == 2 || mode == 4; }
+// (5, 6: lane = triangle with the warp's rays two at a time from a per-warp scratch.  Measured and dropped from the
+// kernel -- tools/sweep_probe.cu variant 6 keeps the loop: 31.7 clocks per (warp, 32 pairs) alone against 35.2 for
+// mode 3, but 3.88 ms against 3.54 ms in the C4 path kernel; the layout helpers below still describe it.)
+__host__ __device__ constexpr bool mode_packed(int mode) { return mode == 3 || mode == 4; }
+__host__ __device__ constexpr bool mode_transposed(int mode) { return mode == 5 || mode == 6; }
+__host__ __device__ constexpr bool mode_verify(int mode) { return mode == 2 || mode == 4 || mode == 6; }
 
 // Quick records of n triangles, in float4: 4 per triangle (MODE 1, 2), or 9 per PAIR of consecutive triangles
 // (MODE 3, 4): float4 j of a pair holds {slot 2j of the even triangle, slot 2j of the odd one, slot 2j+1 of the even
@@ -67,21 +74,32 @@ __host__ __device__ constexpr bool mode_verify(int mode) { return mode == 2 || m
 // that read different pairs (cooperative sweep) are then 36 words apart and an LDS.128 of a quarter warp is free of
 // bank conflicts.  An odd count is completed by a record that drops every ray (thr = +inf).
 constexpr int QPAIR_F4 = 9;
+// MODE 5, 6: 5 float4 per triangle (4 + padding): lane j reads triangle j's record, 20 words apart -- an LDS.128 of a
+// quarter warp touches every bank once.
+constexpr int QTRI_F4 = 5;
+__host__ __device__ constexpr int mode_layout(int mode) { return mode_packed(mode) ? 2 : (mode_transposed(mode) ? 3 : (mode ? 1 : 0)); }
 __host__ __device__ constexpr size_t path_q_f4(int mode, int n)
 {
-    return mode == 0 ? 0 : (mode_packed(mode) ? (size_t)QPAIR_F4 * (size_t)((n + 1) / 2) : (size_t)4 * (size_t)n);
+    return mode == 0 ? 0
+                     : (mode_packed(mode) ? (size_t)QPAIR_F4 * (size_t)((n + 1) / 2)
+                                          : (size_t)(mode_transposed(mode) ? QTRI_F4 : 4) * (size_t)n);
 }
-// float index of slot s (0..15) of triangle i's record
-__host__ __device__ constexpr size_t path_q_slot(bool packed, int i, int s)
+// float index of slot s (0..15) of triangle i's record in layout 1 (per triangle), 2 (per pair), 3 (per triangle, padded)
+__host__ __device__ constexpr size_t path_q_slot(int layout, int i, int s)
 {
-    return packed ? (size_t)(i >> 1) * (4 * QPAIR_F4) + (size_t)((s >> 1) * 4 + (s & 1) * 2 + (i & 1)) : (size_t)i * 16 + s;
+    return layout == 2 ? (size_t)(i >> 1) * (4 * QPAIR_F4) + (size_t)((s >> 1) * 4 + (s & 1) * 2 + (i & 1))
+                       : (size_t)i * (layout == 3 ? 4 * QTRI_F4 : 16) + s;
 }
+// per-warp scratch of the transposed sweep: the warp's 32 rays, two per slot: {dx dx' dy dy'}{dz dz' mx mx'}{my my' mz mz'}
+// + the survivor masks of a chunk, 16 x {ray 2k, ray 2k + 1}
+constexpr int PATH_SCRATCH_F4 = 16 * 3 + 8;
 
 // shared memory (per stage when streaming): [quick records of the stage's triangles][geometry, 3 float4 per triangle]
 __host__ __device__ inline size_t path_smem_bytes(int ntris, bool stream, int mode)
 {
     const int n = stream ? PATH_TILE : (ntris > 0 ? ntris : 1);
-    return (stream ? 2 : 1) * (path_q_f4(mode, n) + (size_t)3 * n) * sizeof(float4);
+    return ((stream ? 2 : 1) * (path_q_f4(mode, n) + (size_t)3 * n) +
+            (mode_transposed(mode) ? (size_t)PATH_SCRATCH_F4 * (PATH_THREADS / 32) : 0)) * sizeof(float4);
 }
 
 // The reference's ray-triangle test arranged for SIMT, in two phases per chunk of 32 triangles.
@@ -169,7 +187,7 @@ __device__ __forceinline__ void tri_quick_bit(const f3 &o, const f3 &d, const fl
 constexpr float QUICK_DBOUND = 1.0625f;
 constexpr float QUICK_EPS = 0.0009999f; // just below the reference's 0.001f
 
-__global__ void quick_records_kernel(const float4 *__restrict__ geo, int n, float obound, float4 *__restrict__ q, int packed)
+__global__ void quick_records_kernel(const float4 *__restrict__ geo, int n, float obound, float4 *__restrict__ q, int layout)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n)
@@ -214,11 +232,11 @@ __global__ void quick_records_kernel(const float4 *__restrict__ geo, int n, floa
     float *qf = reinterpret_cast<float *>(q);
 #pragma unroll
     for (int s = 0; s < 16; ++s)
-        qf[path_q_slot(packed != 0, i, s)] = v[s];
-    if (packed && i == n - 1 && (n & 1)) { // the pair's missing triangle: a record that drops every ray
+        qf[path_q_slot(layout, i, s)] = v[s];
+    if (layout == 2 && i == n - 1 && (n & 1)) { // the pair's missing triangle: a record that drops every ray
 #pragma unroll
         for (int s = 0; s < 16; ++s)
-            qf[path_q_slot(true, n, s)] = s == 15 ? __int_as_float(0x7f800000) : 0.f;
+            qf[path_q_slot(2, n, s)] = s == 15 ? __int_as_float(0x7f800000) : 0.f;
     }
 }
 
@@ -409,6 +427,23 @@ __device__ __forceinline__ void quick_keep_bit(const QuickVals &v, unsigned &m)
         : "f"(v.U), "f"(nM), "f"(v.V), "f"(v.sum), "f"(v.hi), "f"(v.det), "f"(v.M), "f"(v.thr), "n"(BIT));
 }
 
+// the same chain of compares, voted over the warp (lane = triangle): the ray's survivor mask
+__device__ __forceinline__ unsigned quick_keep_ballot(const QuickVals &v)
+{
+    const float nM = -v.M;
+    unsigned b;
+    asm volatile("{\n\t.reg .pred p;\n\t"
+                 "setp.geu.f32 p, %1, %2;\n\t"
+                 "setp.geu.and.f32 p, %3, %2, p;\n\t"
+                 "setp.leu.and.f32 p, %4, %5, p;\n\t"
+                 "setp.leu.or.f32 p, %6, %7, p;\n\t"
+                 "setp.geu.and.f32 p, %6, %8, p;\n\t"
+                 "vote.sync.ballot.b32 %0, p, 0xffffffff;\n\t}"
+                 : "=r"(b)
+                 : "f"(v.U), "f"(nM), "f"(v.V), "f"(v.sum), "f"(v.hi), "f"(v.det), "f"(v.M), "f"(v.thr));
+    return b;
+}
+
 // K-th .. (N-1)-th PAIR of a group of N consecutive pair records: bits 2K, 2K+1 of mg
 template <int K, int N>
 __device__ __forceinline__ void quick2_pairs(const QuickRay2 &r, const float4 *P, unsigned &mg)
@@ -444,7 +479,7 @@ __device__ __forceinline__ bool quick_ray_ok(const f3 &o, const f3 &d, float obo
 // MODE 1: S = quick-record tile (4 float4 per triangle), geo = geometry tile of the same triangles (phase 2).
 // MODE 3: S = pair-record tile (QPAIR_F4 float4 per two triangles), packed quick test.
 // MODE 2, 4: MODE 1, 3 + every pair also runs the exact test; an accepted pair the quick test dropped is counted (viol).
-template <int MODE>
+template <int MODE, int UNROLL = RTC_QUICK_UNROLL>
 __device__ __forceinline__ void sweep_chunked(const float4 *S, const float4 *geo, float obound, int n, int base,
                                               bool active, const f3 &o, const f3 &d, float &best, int &bestId,
                                               unsigned &viol)
@@ -475,7 +510,7 @@ __device__ __forceinline__ void sweep_chunked(const float4 *S, const float4 *geo
                     m |= m1 << j;
                 }
             } else if (mode_packed(MODE)) {
-                constexpr int UP = RTC_QUICK_UNROLL >= 2 ? RTC_QUICK_UNROLL / 2 : 1; // pairs per iteration
+                constexpr int UP = UNROLL >= 2 ? UNROLL / 2 : 1; // pair records per iteration
                 const float4 *P = S + QPAIR_F4 * (c0 >> 1);
                 const int np = (cn + 1) >> 1;
                 int j = 0;
@@ -494,7 +529,7 @@ __device__ __forceinline__ void sweep_chunked(const float4 *S, const float4 *geo
                 if (cn < 32)
                     m &= (1u << cn) - 1u; // an odd count's last pair is completed by a record that never survives
             } else {
-                constexpr int UN = RTC_QUICK_UNROLL;
+                constexpr int UN = UNROLL < 4 ? UNROLL : 4;
                 int j = 0;
                 for (; j + UN <= cn; j += UN) {
                     unsigned mg = 0;
@@ -576,10 +611,11 @@ __device__ __forceinline__ void coop_tile(CoopCtx &c, const float4 *S_, const fl
                 tri_test_exact<false>(c.o, c.d, geo[3 * j + 3], geo[3 * j + 4], geo[3 * j + 5], base + j + 1, c.best, c.id, dummy);
         }
     } else {
+        constexpr int QS = mode_transposed(MODE) ? QTRI_F4 : 4;
         const bool rayok = quick_ray_ok(c.o, c.d, obound);
         const QuickRay qr = quick_ray(c.o, c.d);
         for (int j = c.r; j < n; j += c.S)
-            if (!rayok || tri_quick2(qr, S_[4 * j], S_[4 * j + 1], S_[4 * j + 2], S_[4 * j + 3]))
+            if (!rayok || tri_quick2(qr, S_[QS * j], S_[QS * j + 1], S_[QS * j + 2], S_[QS * j + 3]))
                 tri_test_exact<false>(c.o, c.d, geo[3 * j], geo[3 * j + 1], geo[3 * j + 2], base + j, c.best, c.id, dummy);
     }
 }
@@ -590,7 +626,7 @@ __device__ __forceinline__ void coop_tile(CoopCtx &c, const float4 *S_, const fl
 // (the group instantiation is capped at the registers of PATH_GROUP_CTAS CTAs per SM and launched with exactly that
 // grid: its S is chosen for a fully resident grid)
 template <bool STREAM, int MODE, bool GROUPS>
-__global__ void __launch_bounds__(PATH_THREADS, GROUPS ? PATH_GROUP_CTAS : ((MODE == 3 && !STREAM) ? 6 : RTC_PATH_MINB)) render_paths_kernel(const RenderArgs a, const PathWork w)
+__global__ void __launch_bounds__(PATH_THREADS, GROUPS ? PATH_GROUP_CTAS : (MODE == 3 ? (STREAM ? 5 : RTC_PATH_MINB3) : RTC_PATH_MINB)) render_paths_kernel(const RenderArgs a, const PathWork w)
 {
     {
         const unsigned np = w.list ? *w.list_count : (unsigned)(a.out_w * a.out_h);
@@ -944,7 +980,7 @@ __global__ void __launch_bounds__(PATH_THREADS, GROUPS ? PATH_GROUP_CTAS : ((MOD
                 if (coop || grouped)
                     coop_tile<MODE>(cc, stage, stage + qoff, w.obound, min(tile, ntris - t * tile), t * tile);
                 else
-                    sweep_chunked<MODE>(stage, stage + qoff, w.obound, min(tile, ntris - t * tile), t * tile,
+                    sweep_chunked<MODE, 4>(stage, stage + qoff, w.obound, min(tile, ntris - t * tile), t * tile,
                                         sweeping, L.pos, L.dir, best, bestId, viol);
                 __syncthreads(); // every warp is done with this stage
                 if (threadIdx.x == 0 && t + 2 < ntiles)

@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 @pytest.fixture(autouse=True, params=["packed", "scalar"])
 def quick_layout(request, monkeypatch):
     """Both evaluations of the quick records: two triangles at a time with packed FP32 (default), one at a time."""
-    monkeypatch.setenv("RTC_QUICK_PACKED", "1" if request.param == "packed" else "0")
+    monkeypatch.setenv("RTC_QUICK_FORM", {"packed": "3", "scalar": "1"}[request.param])
     return request.param
 
 

@@ -45,11 +45,11 @@ def test_streamed_tiles_bit_identical(small_tiles, name):
 
 
 @pytest.mark.parametrize("name", NAMES[:3])
-@pytest.mark.parametrize("packed,tile", [("0", "24"), ("0", "23"), ("1", "23"), ("1", "2")])
-def test_streamed_tiles_record_layouts(small_tiles, monkeypatch, name, packed, tile):
-    """Both quick-record layouts (per triangle / per pair for the packed FP32 evaluation) through the TMA tiles;
-    an odd tile request is rounded up to a whole pair in the packed layout."""
-    monkeypatch.setenv("RTC_QUICK_PACKED", packed)
+@pytest.mark.parametrize("form,tile", [("1", "24"), ("1", "23"), ("3", "23"), ("3", "2")])
+def test_streamed_tiles_record_layouts(small_tiles, monkeypatch, name, form, tile):
+    """Both quick-record layouts (per triangle / per pair for the packed FP32 evaluation) through the TMA tiles; an
+    odd tile request is rounded up to a whole pair in the packed layout."""
+    monkeypatch.setenv("RTC_QUICK_FORM", form)
     monkeypatch.setenv("RTC_PATH_TILE", tile)
     _render_and_check(name)
 

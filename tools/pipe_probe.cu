@@ -14,7 +14,8 @@ __global__ void __launch_bounds__(256) probe(float *out, float a, float b, int n
     float r[NCH];
     unsigned u[NCH];
     __half2 h[NCH], hs = __floats2half2_rn(a, b);
-    unsigned long long p2[NCH];
+    unsigned long long p2[NCH], bb;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(bb) : "f"(a), "f"(b + threadIdx.x));
 #pragma unroll
     for (int k = 0; k < NCH; ++k) {
         r[k] = threadIdx.x + k;
@@ -48,6 +49,13 @@ __global__ void __launch_bounds__(256) probe(float *out, float a, float b, int n
             if (MODE == 9) u[k] = max(u[k], u[(k + 1) % NCH]);            // IMNMX / VIMNMX (alu)
             if (MODE == 10) r[k] = fmaxf(r[k], r[(k + 1) % NCH]);         // FMNMX (alu)
             if (MODE == 11) asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(p2[k]) : "l"(p2[(k + 1) % NCH]), "l"(p2[(k + 2) % NCH])); // FFMA2 3-reg
+            if (MODE == 17) asm volatile("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(p2[k]) : "l"(p2[(k + 1) % NCH]), "l"(bb)); // FFMA2 acc, reg64, SAME reg64 (reuse)
+            if (MODE == 18) { unsigned long long bk; asm("mov.b64 %0, {%1, %1};" : "=l"(bk) : "f"(r[k])); // FFMA2 acc, reg64, per-k .F32 broadcast
+                asm volatile("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(p2[k]) : "l"(p2[(k + 1) % NCH]), "l"(bk)); }
+            if (MODE == 19) { unsigned long long bk; asm("mov.b64 %0, {%1, %1};" : "=l"(bk) : "f"(r[0])); // FFMA2 acc, reg64, SAME .F32 broadcast
+                asm volatile("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(p2[k]) : "l"(p2[(k + 1) % NCH]), "l"(bk)); }
+            if (MODE == 20) r[k] = fmaf(r[(k + 3) % NCH], a, r[k]);       // FFMA acc, reg, const
+            if (MODE == 21) r[k] = fmaf(r[(k + 3) % NCH], r[(k + 5) % NCH], r[k]); // FFMA acc, reg, reg (other spacing)
             if (MODE == 12) {                                             // FFMA2 + FMNMX alternating (fma pipe + alu pipe)
                 asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(p2[k]) : "l"(p2[(k + 1) % NCH]), "l"(p2[(k + 2) % NCH]));
                 r[k] = fmaxf(r[k], r[(k + 1) % NCH]);
@@ -120,6 +128,11 @@ int main()
     run<9>("IMNMX", NCH);
     run<10>("FMNMX", NCH);
     run<11>("FFMA2 r,r,r (warp-inst; x2 FMA each)", NCH);
+    run<17>("FFMA2 acc, r64, same r64", NCH);
+    run<18>("FFMA2 acc, r64, per-instr .F32 broadcast", NCH);
+    run<19>("FFMA2 acc, r64, same .F32 broadcast", NCH);
+    run<20>("FFMA acc, r, c", NCH);
+    run<21>("FFMA acc, r, r", NCH);
     run<12>("FFMA2 + FMNMX alternating", 2 * NCH);
     run<13>("FFMA + IMNMX alternating", 2 * NCH);
     run<14>("FFMA2 + FFMA alternating", 2 * NCH);

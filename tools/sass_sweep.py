@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Extract the branch-free first phase of the path kernel's sweep (the hot loop) from the built library's SASS.
 
-usage: python tools/sass_sweep.py [MODE] > profiles/rNN_sass_sweep.txt      (MODE 1 = quick records, 0 = reference arithmetic)
+usage: python tools/sass_sweep.py [MODE] > profiles/rNN_sass_sweep.txt   (MODE 3 = packed quick records, 1 = scalar quick records, 0 = reference arithmetic)
 The loop is found as the call-free, convergence-barrier-free backward branch whose body has the most FP32 arithmetic."""
 import os
 import re
@@ -9,7 +9,7 @@ import subprocess
 import sys
 from collections import Counter
 
-mode = sys.argv[1] if len(sys.argv) > 1 else "1"
+mode = sys.argv[1] if len(sys.argv) > 1 else "3"
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 lib = os.path.join(root, "raytracingc_b200", "librtc_b200.so")
 txt = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True, check=True).stdout
@@ -36,12 +36,17 @@ ops = Counter()
 for l in body:
     t = re.sub(r"/\*[0-9a-f]+\*/", "", l).split()
     ops[(t[1] if t[0].startswith("@") else t[0]).split(".")[0]] += 1
-per = 4
+per = max(1, ops["LDS"] // (3 if mode == "0" else 4))  # 4 LDS.128 of quick record per triangle (3 of geometry in mode 0)
 print(f"render_paths_kernel<false, {mode}> (sm_100a, cuobjdump -sass of raytracingc_b200/librtc_b200.so): the branch-free")
 print(f"first phase of sweep_chunked (rtc_paths.cuh), {per} triangles per iteration: {len(body)} instructions = "
       f"{len(body) / per:.2f} per (ray, triangle) pair.")
-print("Per-triangle data by warp-uniform LDS.128; survivors set one bit of the lane's mask through a chained predicate")
-print("(FSETP ... .AND/.OR P) and a predicated add; phase 2 (tri_test_exact on the survivors) follows the loop.")
+if mode in ("3", "4"):
+    print("Two triangles per packed instruction (FFMA2 / FMUL2 / FADD2 on pair-interleaved records, the ray's scalars as the")
+    print("broadcast operand Rx.F32); per-pair data by warp-uniform LDS.128; survivors set one bit of the lane's mask through")
+    print("a chained predicate (FSETP ... .AND/.OR P) and a predicated add; phase 2 (tri_test_exact) follows the loop.")
+else:
+    print("Per-triangle data by warp-uniform LDS.128; survivors set one bit of the lane's mask through a chained predicate")
+    print("(FSETP ... .AND/.OR P) and a predicated add; phase 2 (tri_test_exact on the survivors) follows the loop.")
 print("opcode counts: " + ", ".join(f"{k} {v}" for k, v in ops.most_common()))
 print()
 print("\n".join(body))

@@ -22,8 +22,8 @@ template <int V>
 __global__ void __launch_bounds__(128, 6) probe(const float4 *__restrict__ qrec, int n, int reps, unsigned *out)
 {
     extern __shared__ float4 sQ[];
-    const int nq = (int)path_q_f4((V == 0 || V == 3) ? 1 : 3, n);
-    if (V < 2 || V == 4) {
+    const int nq = (int)path_q_f4((V == 0 || V == 3) ? 1 : (V == 6 ? 5 : 3), n);
+    if (V < 2 || V >= 4) {
         for (int i = threadIdx.x; i < nq; i += blockDim.x)
             sQ[i] = qrec[i];
         __syncthreads();
@@ -36,7 +36,7 @@ __global__ void __launch_bounds__(128, 6) probe(const float4 *__restrict__ qrec,
     for (int r = 0; r < reps; ++r) {
         const QuickRay qr = quick_ray(o, d);
         const QuickRay2 qr2 = quick_ray2(qr);
-        for (int c0 = 0; c0 < n; c0 += 32) {
+        for (int c0 = 0; c0 < n && V < 5; c0 += 32) {
             const int cn = min(32, n - c0);
             unsigned m = 0;
             if (V == 0 || V == 3) {
@@ -84,6 +84,79 @@ __global__ void __launch_bounds__(128, 6) probe(const float4 *__restrict__ qrec,
             }
             acc += __popc(m);
         }
+        if (V == 6) { // lane = triangle, rays two at a time from a per-warp scratch (MODE 5 of the kernel, first phase only)
+            const int lane = threadIdx.x & 31;
+            float4 *scr = sQ + QTRI_F4 * n + PATH_SCRATCH_F4 * (threadIdx.x >> 5);
+            float *sf = reinterpret_cast<float *>(scr) + 12 * (lane >> 1) + (lane & 1);
+            sf[0] = qr.d.x, sf[2] = qr.d.y, sf[4] = qr.d.z, sf[6] = qr.m.x, sf[8] = qr.m.y, sf[10] = qr.m.z;
+            uint2 *msk = reinterpret_cast<uint2 *>(scr + 16 * 3);
+            __syncwarp();
+            const f32x2 kk = pk2(1.0000019073486328f, 1.0000019073486328f);
+            for (int c0 = 0; c0 < n; c0 += 32) {
+                const int cn = min(32, n - c0);
+                float4 r0 = make_float4(0.f, 0.f, 0.f, 0.f), r1 = r0, r2 = r0, r3 = make_float4(0.f, 0.f, 0.f, __int_as_float(0x7f800000));
+                if (lane < cn) {
+                    const float4 *R = sQ + QTRI_F4 * (c0 + lane);
+                    r0 = R[0], r1 = R[1], r2 = R[2], r3 = R[3];
+                }
+                QuickVals v0, v1;
+                v0.thr = v1.thr = r3.w;
+                v0.M = v1.M = QUICK_EPS - r3.w;
+                const f32x2 M2 = pk2(v0.M, v0.M);
+                const f32x2 c0x = pk2(r0.x, r0.x), c0y = pk2(r0.y, r0.y), c0z = pk2(r0.z, r0.z), c0w = pk2(r0.w, r0.w);
+                const f32x2 c1x = pk2(r1.x, r1.x), c1y = pk2(r1.y, r1.y), c1z = pk2(r1.z, r1.z), c1w = pk2(r1.w, r1.w);
+                const f32x2 c2x = pk2(r2.x, r2.x), c2y = pk2(r2.y, r2.y), c2z = pk2(r2.z, r2.z), c2w = pk2(r2.w, r2.w);
+                const f32x2 c3x = pk2(r3.x, r3.x), c3y = pk2(r3.y, r3.y), c3z = pk2(r3.z, r3.z);
+                auto slot = [&](int k) {
+                    const ulonglong2 *Q = reinterpret_cast<const ulonglong2 *>(scr + 3 * k);
+                    const ulonglong2 qa = Q[0], qb = Q[1], qc = Q[2];
+                    const f32x2 U = fma2(c1y, qb.x, fma2(c1x, qa.y, fma2(c0w, qa.x, fma2(c0z, qc.y, fma2(c0y, qc.x, mul2(c0x, qb.y))))));
+                    const f32x2 Vv = fma2(c2w, qb.x, fma2(c2z, qa.y, fma2(c2y, qa.x, fma2(c2x, qc.y, fma2(c1w, qc.x, mul2(c1z, qb.y))))));
+                    const f32x2 det = fma2(c3z, qb.x, fma2(c3y, qa.y, mul2(c3x, qa.x)));
+                    const f32x2 sum = add2(U, Vv);
+                    const f32x2 hi = fma2(det, kk, M2);
+                    unpk2(U, v0.U, v1.U);
+                    unpk2(Vv, v0.V, v1.V);
+                    unpk2(det, v0.det, v1.det);
+                    unpk2(sum, v0.sum, v1.sum);
+                    unpk2(hi, v0.hi, v1.hi);
+                    const unsigned b0 = quick_keep_ballot(v0), b1 = quick_keep_ballot(v1);
+                    if (lane == 0)
+                        msk[k] = make_uint2(b0, b1);
+                };
+#pragma unroll 1
+                for (int k = 0; k < 16; k += 2) {
+                    slot(k);
+                    slot(k + 1);
+                }
+                __syncwarp();
+                acc += __popc(reinterpret_cast<const unsigned *>(msk)[lane]);
+                __syncwarp();
+            }
+        }
+        if (V == 5) { // two rays per lane: every pair record is loaded once for both
+            f3 o2 = mk3(o.y, o.z, o.x), d2 = mk3(d.y, d.x, d.z);
+            const QuickRay2 qb = quick_ray2(quick_ray(o2, d2));
+            for (int c0 = 0; c0 < n; c0 += 32) {
+                const int np = (min(32, n - c0) + 1) >> 1;
+                unsigned ma = 0, mb = 0;
+#pragma unroll 1
+                for (int j = 0; j < np; ++j) {
+                    const float4 *P = sQ + QPAIR_F4 * ((c0 >> 1) + j);
+                    QuickVals v0, v1, w0, w1;
+                    quick_vals2(qr2, P, v0, v1);
+                    quick_vals2(qb, P, w0, w1);
+                    unsigned mg = 0, mh = 0;
+                    quick_keep_bit<1u>(v0, mg);
+                    quick_keep_bit<2u>(v1, mg);
+                    quick_keep_bit<1u>(w0, mh);
+                    quick_keep_bit<2u>(w1, mh);
+                    ma |= mg << (2 * j);
+                    mb |= mh << (2 * j);
+                }
+                acc += __popc(ma) + __popc(mb);
+            }
+        }
         o.x += 1e-4f; // the next "ray": keeps the sweep from being hoisted out of the loop
         d.y += 1e-5f;
     }
@@ -109,29 +182,33 @@ int main(int argc, char **argv)
         geo[3 * i + 1] = make_float4(e1[0], e1[1], e1[2], ny);
         geo[3 * i + 2] = make_float4(e2[0], e2[1], e2[2], nz);
     }
-    float4 *dgeo, *q1, *q2;
+    float4 *dgeo, *q1, *q2, *q3;
     unsigned *out;
     const int blocks = sms * 6, threads = 128;
     cudaMalloc(&dgeo, sizeof(float4) * 3 * n);
     cudaMalloc(&q1, sizeof(float4) * (path_q_f4(1, n) + 16));
     cudaMalloc(&q2, sizeof(float4) * (path_q_f4(3, n) + 16));
     cudaMalloc(&out, sizeof(unsigned) * blocks * threads);
+    cudaMalloc(&q3, sizeof(float4) * (path_q_f4(5, n) + 16));
     cudaMemcpy(dgeo, geo.data(), sizeof(float4) * 3 * n, cudaMemcpyHostToDevice);
-    quick_records_kernel<<<(n + 127) / 128, 128>>>(dgeo, n, 4.0f, q1, 0);
-    quick_records_kernel<<<(n + 127) / 128, 128>>>(dgeo, n, 4.0f, q2, 1);
+    quick_records_kernel<<<(n + 127) / 128, 128>>>(dgeo, n, 4.0f, q1, 1);
+    quick_records_kernel<<<(n + 127) / 128, 128>>>(dgeo, n, 4.0f, q2, 2);
+    quick_records_kernel<<<(n + 127) / 128, 128>>>(dgeo, n, 4.0f, q3, 3);
     cudaDeviceSynchronize();
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0);
     cudaEventCreate(&e1);
     std::vector<unsigned> h(blocks * threads);
-    unsigned long long sums[5] = {0, 0, 0, 0, 0};
-    const char *names[5] = {"scalar FFMA, LDS.128 records", "packed FFMA2, LDS.128 pair records",
+    unsigned long long sums[7] = {0, 0, 0, 0, 0, 0, 0};
+    const char *names[7] = {"scalar FFMA, LDS.128 records", "packed FFMA2, LDS.128 pair records",
                             "packed FFMA2, __constant__ pair records (uniform operand)",
                             "scalar FFMA, __constant__ records (uniform operand)",
-                            "packed FFMA2 ordered by ray component (operand reuse), LDS.128"};
-    for (int v = 0; v < 5; ++v) {
-        const bool pk = v == 1 || v == 2 || v == 4;
-        const size_t qf4 = path_q_f4(pk ? 3 : 1, n);
+                            "packed FFMA2 ordered by ray component (operand reuse), LDS.128",
+                            "packed FFMA2, TWO rays per lane share each LDS.128 (per ray)",
+                            "lane = triangle, packed FFMA2 over two rays (scratch)"};
+    for (int v = 0; v < 7; ++v) {
+        const bool pk = v == 1 || v == 2 || v == 4 || v == 5;
+        const size_t qf4 = path_q_f4(v == 6 ? 5 : (pk ? 3 : 1), n);
         if (v == 2 || v == 3) {
             if (qf4 > CQ_F4) {
                 printf("%-62s skipped (records exceed the constant space)\n", names[v]);
@@ -139,17 +216,21 @@ int main(int argc, char **argv)
             }
             cudaMemcpyToSymbol(cq, pk ? q2 : q1, sizeof(float4) * qf4, 0, cudaMemcpyDeviceToDevice);
         }
-        const size_t smem = (v < 2 || v == 4) ? sizeof(float4) * qf4 : 0;
+        const size_t smem = (v < 2 || v >= 4) ? sizeof(float4) * (qf4 + (v == 6 ? PATH_SCRATCH_F4 * 4 : 0)) : 0;
         auto launch = [&]() {
             if (v == 0) probe<0><<<blocks, threads, smem>>>(q1, n, reps, out);
             if (v == 1) probe<1><<<blocks, threads, smem>>>(q2, n, reps, out);
             if (v == 2) probe<2><<<blocks, threads, smem>>>(q2, n, reps, out);
             if (v == 3) probe<3><<<blocks, threads, smem>>>(q1, n, reps, out);
             if (v == 4) probe<4><<<blocks, threads, smem>>>(q2, n, reps, out);
+            if (v == 5) probe<5><<<blocks, threads, smem>>>(q2, n, reps, out);
+            if (v == 6) probe<6><<<blocks, threads, smem>>>(q3, n, reps, out);
         };
         if (v == 0) cudaFuncSetAttribute(probe<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (v == 1) cudaFuncSetAttribute(probe<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (v == 4) cudaFuncSetAttribute(probe<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (v == 5) cudaFuncSetAttribute(probe<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (v == 6) cudaFuncSetAttribute(probe<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         float best = 1e30f;
         for (int rep = 0; rep < 4; ++rep) {
             cudaEventRecord(e0);
@@ -169,8 +250,8 @@ int main(int argc, char **argv)
         cudaMemcpy(h.data(), out, sizeof(unsigned) * h.size(), cudaMemcpyDeviceToHost);
         for (unsigned x : h)
             sums[v] += x;
-        const int nn = n & ~3; // triangles the unrolled loops cover
-        const double pairs = (double)blocks * threads * reps * nn;
+        const int nn = v == 6 ? n : (n & ~3); // triangles the unrolled loops cover
+        const double pairs = (double)blocks * threads * reps * nn * (v == 5 ? 2 : 1);
         const double clk_per_pair_warp = best * 1e-3 * khz * 1e3 * sms * 4 / (pairs / 32);
         printf("%-62s %8.3f ms  %.3e pairs/s  %5.2f SMSP-clocks per (warp, triangle)  survivors %llu\n", names[v], best,
                pairs / (best * 1e-3), clk_per_pair_warp, sums[v]);
