@@ -114,7 +114,11 @@ __device__ __noinline__ float4 random_direction(uint32_t state)
     // one copy of the FP64 code executed three times: the smaller instruction footprint beats the overlap of three
     // inlined chains (measured, C4 path kernel: 4.15 -> 3.95 ms; the shading code is instruction-fetch bound)
     float x = 0.f, y = 0.f, z = 0.f;
+#ifdef RTC_NORMALS_UNROLLED
+#pragma unroll
+#else
 #pragma unroll 1
+#endif
     for (int i = 0; i < 3; ++i) {
         x = y;
         y = z;
@@ -133,7 +137,20 @@ struct SkyParams {
 
 // glibc's powf is < 1 ulp; CUDA's powf is several ulp, so evaluate in double
 // and narrow.
-__device__ __noinline__ float xpowf(float x, float y) { return (float)pow((double)x, (double)y); }
+// The double-precision evaluation only has to be far more accurate than a float ulp (glibc's own powf is off by up to
+// ~0.52 ulp, so agreement in the last bit is statistical either way): for a finite positive base and a finite
+// non-zero exponent it is exp2(y * log2(x)) in plain double -- relative error ~2^-46 for |y log2 x| < 64, i.e. one
+// more float in 2^21 rounded differently than by the exactly rounded power -- which is a third of the instructions
+// of CUDA's double pow (that one carries log2(x) in double-double to be accurate to 2 ulp OF A DOUBLE).  Everything
+// else (zero, infinite, negative or NaN base, zero exponent) takes pow() itself.
+__device__ __noinline__ float xpowf(float x, float y)
+{
+#ifndef RTC_POW_LIBM
+    if (x > 0.0f && x < __int_as_float(0x7f800000) && y != 0.0f && fabsf(y) < 1e30f)
+        return (float)exp2((double)y * log2((double)x));
+#endif
+    return (float)pow((double)x, (double)y);
+}
 
 // Two exact shortcuts around the powf calls (the most expensive instructions of a miss):
 //  * powf(+0, .35) = +0 and powf(1, .35) = 1 exactly (smoothstep clamps, so below the horizon line and above
