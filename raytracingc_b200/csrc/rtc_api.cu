@@ -605,7 +605,9 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
     if (per_sm_g < 1)
         return fail(RTC_ERR_CUDA, "path kernel (group mode) does not fit on an SM (smem %zu)", smem);
     const int blocks_g = sc->nsm * std::min(per_sm_g, rtc::PATH_GROUP_CTAS);
-    w.group_lanes = (unsigned)blocks_g * rtc::PATH_THREADS;
+    // RTC_GROUP_OVERSUB (percent, default 100): let the group mode count on more lanes than are resident -- groups then
+    // take their pixels in more than one wave (A/B knob for frames split over 2-4 GPUs)
+    w.group_lanes = (unsigned)((unsigned long long)blocks_g * rtc::PATH_THREADS * (unsigned)std::max(1, env_int("RTC_GROUP_OVERSUB", 100)) / 100u);
     kern<<<blocks, rtc::PATH_THREADS, smem, st>>>(a, w);
     kern_groups<<<blocks_g, rtc::PATH_THREADS, smem, st>>>(a, w);
     CU(cudaGetLastError());
