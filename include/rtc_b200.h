@@ -210,6 +210,14 @@ int rtc_render_launch_count(const RtcScene *scene, const RtcDeviceJob *job, int 
 int rtc_uninterleave_device(int device, const void *d_parts, void *d_img, int elem_size, int row_elems, int height,
                             int nparts, int band_h, size_t part_elems, void *stream);
 
+/* One part of a band split (the rows rtc_render_device wrote for RtcSubset{part * band_h, nparts * band_h, 0, 1, band_h},
+ * compact, band after band) straight into a HOST image of `height` rows of `row_bytes` bytes, asynchronously on
+ * `stream`: one strided device->host copy.  With one process or thread per GPU every device delivers its own rows
+ * over its own PCIe link -- the all-gather + rtc_uninterleave_device + full-frame copy are only needed when the frame
+ * is wanted in DEVICE memory.  (The reference's row threads fill `Color image[]` the same way: main.c:84,100.) */
+int rtc_download_bands(int device, const void *d_part, void *h_img, size_t row_bytes, int height, int nparts, int band_h,
+                       int part, void *stream);
+
 /* Dependent-free FFMA probe: measured FP32 peak of `device` in TFLOP/s (2 flop per FFMA), best of `reps`.
  * The roofline denominator of the intersection kernel (MEASURED_PEAKS.json has no FP32 figure). */
 int rtc_fp32_peak_probe(int device, int reps, double *tflops, double *ms_best);

@@ -91,7 +91,7 @@ _lib = None
 EXPORTS = ["render_cuda", "render_cuda_shutdown", "rtc_camera_look_at", "rtc_normalize", "rtc_device_count",
            "rtc_last_error", "rtc_version", "rtc_scene_create", "rtc_scene_destroy", "rtc_subset_size",
            "rtc_render_device", "rtc_sum_quantize_device", "rtc_quantize_device", "rtc_render_launch_count",
-           "rtc_uninterleave_device", "rtc_fp32_peak_probe", "rtc_scene_update", "rtc_scene_kernel_times", "rtc_synth_scene",
+           "rtc_uninterleave_device", "rtc_download_bands", "rtc_fp32_peak_probe", "rtc_scene_update", "rtc_scene_kernel_times", "rtc_synth_scene",
            "rtc_probe_random_direction", "rtc_probe_environment_light"]
 
 
@@ -144,6 +144,9 @@ def load_library() -> C.CDLL:
     lib.rtc_uninterleave_device.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                             C.c_int, C.c_size_t, C.c_void_p]
     lib.rtc_uninterleave_device.restype = C.c_int
+    lib.rtc_download_bands.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int,
+                                       C.c_void_p]
+    lib.rtc_download_bands.restype = C.c_int
     lib.rtc_scene_kernel_times.argtypes = [C.c_void_p, P(C.c_float), P(C.c_float)]
     lib.rtc_scene_kernel_times.restype = C.c_int
     lib.rtc_synth_scene.argtypes = [C.c_uint64, C.c_int32, C.c_void_p]
@@ -328,6 +331,13 @@ def uninterleave(device: int, d_parts: int, d_img: int, elem_size: int, row_elem
                  band_h: int, part_elems: int, stream: int = 0):
     _check(load_library().rtc_uninterleave_device(device, d_parts, d_img, elem_size, row_elems, height, nparts,
                                                   band_h, part_elems, stream or None))
+
+
+def download_bands(device: int, d_part: int, h_img: int, row_bytes: int, height: int, nparts: int, band_h: int,
+                   part: int, stream: int = 0):
+    """This part's rows of a band split straight into a host image (asynchronous on `stream`)."""
+    _check(load_library().rtc_download_bands(device, d_part, h_img, row_bytes, height, nparts, band_h, part,
+                                             stream or None))
 
 
 def synth_scene(ntris: int, seed: int = 0xB200) -> np.ndarray:

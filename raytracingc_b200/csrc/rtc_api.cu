@@ -1527,4 +1527,33 @@ int rtc_uninterleave_device(int device, const void *d_parts, void *d_img, int el
     return RTC_OK;
 }
 
+// One part of a band split straight into the caller's HOST image: the part's compact rows (bands part,
+// part + nparts, ... of band_h rows each) go to their image rows with one strided copy (+ one for a cut last band).
+// With one process or thread per GPU every device writes its own rows over its own PCIe link -- no gather, no
+// un-interleave and no full-frame copy through device 0 when the image is wanted in host memory anyway.
+int rtc_download_bands(int device, const void *d_part, void *h_img, size_t row_bytes, int height, int nparts, int band_h,
+                       int part, void *stream)
+{
+    if (!d_part || !h_img || row_bytes == 0 || height <= 0 || nparts <= 0 || band_h <= 0 || part < 0 || part >= nparts)
+        return fail(RTC_ERR_ARG, "download_bands: bad arguments");
+    CU(cudaSetDevice(device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t band_bytes = (size_t)band_h * row_bytes, stride = (size_t)nparts * band_bytes;
+    // bands of this part: rows [b * nparts * band_h + part * band_h, + band_h) for b = 0, 1, ... while inside the image
+    const int first = part * band_h, period = nparts * band_h;
+    if (first >= height)
+        return RTC_OK;
+    const int nb = (height - first + period - 1) / period;                        // bands that start inside the image
+    const int last_rows = std::min(band_h, height - (first + (nb - 1) * period)); // rows of the last one
+    const int nfull = last_rows == band_h ? nb : nb - 1;
+    char *dst = static_cast<char *>(h_img) + (size_t)first * row_bytes;
+    const char *src = static_cast<const char *>(d_part);
+    if (nfull > 0)
+        CU(cudaMemcpy2DAsync(dst, stride, src, band_bytes, band_bytes, (size_t)nfull, cudaMemcpyDeviceToHost, st));
+    if (nfull < nb)
+        CU(cudaMemcpyAsync(dst + (size_t)nfull * stride, src + (size_t)nfull * band_bytes, (size_t)last_rows * row_bytes,
+                           cudaMemcpyDeviceToHost, st));
+    return RTC_OK;
+}
+
 } // extern "C"

@@ -72,3 +72,38 @@ def test_obj_mode_cli_png_and_two_gpus(tmp_path):
     raw = np.frombuffer(zlib.decompress(p[i0 + 4:i0 + 4 + n]), np.uint8).reshape(90, 1 + 160 * 3)[:, 1:].reshape(90, 160, 3)
     want, _ = util.golden_image("suze_160x90_16spp_3b")
     assert (raw == want).all()
+
+
+@pytest.mark.parametrize("name,world", [("suze_odd_101x67_5spp_2b", 2), ("suze_odd_101x67_5spp_2b", 3),
+                                        ("ultracomplex_160x90_16spp_4b", 4), ("default_64x64_16spp_4b", 8)])
+def test_download_bands_assembles_the_frame_on_the_host(name, world):
+    """rtc_download_bands: every part of a band split copied straight to its rows of ONE host image (what each rank
+    of a multi-GPU job does over its own PCIe link) gives the golden frame -- heights that cut the last band,
+    parts without a last band, pinned and pageable host memory."""
+    import torch
+    import raytracingc_b200 as rtc
+    from raytracingc_b200 import api, split
+    from tests import util
+    e = util.kat()[name]
+    job = util.job_of(e)
+    tris = util.scene_tris(e["scene"])
+    want_rgb, _ = util.golden_image(name)
+    kw = util.gpu_kwargs(job)
+    W, H = kw["width"], kw["height"]
+    sc = rtc.DeviceScene(tris, device=0)
+    dev = torch.device("cuda", 0)
+    st = torch.cuda.current_stream()
+    for pinned in (True, False):
+        host = torch.full((H, W, 3), 7, dtype=torch.uint8)
+        if pinned:
+            host = host.pin_memory()
+        for part in range(world):
+            dj = rtc.DeviceJob(W, H, kw["spp"], kw["max_bounce"], triangles_only=kw["triangles_only"],
+                               subset=split.band_subset(part, world))
+            dj.to_c()
+            rgb = torch.zeros((max(dj.out_h, 1), W, 3), dtype=torch.uint8, device=dev)
+            if dj.out_h > 0:
+                sc.render(dj, kw["scene"], kw["camera"], d_rgb=rgb.data_ptr(), stream=st.cuda_stream)
+            api.download_bands(0, rgb.data_ptr(), host.data_ptr(), W * 3, H, world, split.BAND_H, part, st.cuda_stream)
+            torch.cuda.synchronize()
+        assert (host.numpy() == want_rgb).all(), f"{name} world {world} pinned {pinned}"
