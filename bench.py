@@ -310,8 +310,10 @@ def run_ours(a) -> dict:
             shared["frame"] += 1
             shared["flags"][rank] = shared["frame"]  # this rank's rows of frame n are in the host image
             if rank == 0:                            # the caller's view: the frame is complete when every rank says so
+                t_wait = time.perf_counter()
                 while int(shared["flags"].min()) < shared["frame"]:
-                    pass
+                    if time.perf_counter() - t_wait > 30.0:
+                        raise SystemExit("bench.py: a rank did not deliver its rows of the frame within 30 s")
         else:
             dscene.update(host_tris_np, stream=sh)
             launches[0] += 2

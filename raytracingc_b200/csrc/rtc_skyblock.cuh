@@ -24,7 +24,10 @@
 namespace rtc {
 
 constexpr int BLK_W = 8, BLK_H = 4;                 // pixels per lane-block
-constexpr int SKYB_WARPS = 4, SKYB_THREADS = 32 * SKYB_WARPS;
+#ifndef RTC_SKYB_WARPS // warps per CTA of the block kernel (8 KB of hit records each): A/B knob
+#define RTC_SKYB_WARPS 4
+#endif
+constexpr int SKYB_WARPS = RTC_SKYB_WARPS, SKYB_THREADS = 32 * SKYB_WARPS;
 constexpr int SKYB_CHUNK = 32;                      // triangles per candidate mask
 
 __host__ __device__ inline size_t skyblock_smem_bytes(int ntris, bool stream)
