@@ -1155,7 +1155,12 @@ int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const
         if (S % G)
             return fail(RTC_ERR_ARG, "sample split: nsplit (%d) must be a multiple of ngpus (%d)", S, G);
     }
-    if (G > 1) {
+    // Tile split: the caller's image is in HOST memory, so every device copies its own bands straight to their rows
+    // (rtc_download_bands: one strided copy per device, each over its own PCIe link) -- no gather through device 0.
+    // RTC_GATHER=1 keeps the frame's assembly on device 0 (NCCL all-gather over NVLink + un-interleave + one copy);
+    // the sample split always needs it (ordered sum of the sub-stream planes).
+    const bool direct = G > 1 && !samples && env_int("RTC_GATHER", 0) == 0;
+    if (G > 1 && !direct) {
         int rc = ensure_comms(G);
         if (rc)
             return rc;
@@ -1254,7 +1259,7 @@ int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const
     // gather over NVLink + finish on device 0
     DeviceSlot &s0 = g_ctx.slot[base];
     const uint8_t *d_final = static_cast<const uint8_t *>(s0.part);
-    if (G > 1) {
+    if (G > 1 && !direct) {
         NC(g_ctx.nccl.GroupStart());
         for (int g = 0; g < G; ++g) {
             DeviceSlot &s = g_ctx.slot[g];
@@ -1276,7 +1281,15 @@ int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const
     }
     CU(cudaSetDevice(base));
     CU(cudaEventRecord(s0.ev[3], s0.stream));
-    if (pipelined) {
+    if (direct) {
+        for (int g = 0; g < G; ++g) {
+            DeviceSlot &s = g_ctx.slot[base + g];
+            int rc = rtc_download_bands(base + g, s.part, out_rgb, (size_t)W * 3, H, G, BAND_H, g, s.stream);
+            if (rc)
+                return rc;
+        }
+        CU(cudaSetDevice(base));
+    } else if (pipelined) {
         // the copy stream follows the kernels: sky pixels are final after the classification kernel, the rows of
         // a chunk once the path kernel has finished its last primary-hit pixel (flag set on the device;
         // rtc_render_device sets every flag at the end of the frame whatever path it took)
@@ -1349,7 +1362,7 @@ int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const
         st->download_ms = 0; // folded into the caller's wall clock; the copy is asynchronous to ev[3]
         st->ngpus_used = G;
         int per_dev = 1 + (p->ntris > 0) + (p->nspheres > 0) + ((!samples && S > 1) ? 1 : 0);
-        st->kernels_launched = per_dev * G + (G > 1 ? 1 : 0);
+        st->kernels_launched = per_dev * G + (G > 1 && !direct ? 1 : 0);
     }
     if (trace)
         fprintf(stderr, "rtc_b200: render_cuda host timeline: enqueued at %.0f us, synchronised at %.0f us, done at %.0f us\n",

@@ -22,8 +22,12 @@ def gpu_counts(rtc):
     return [g for g in (2, 4, 8) if g <= rtc.device_count()]
 
 
+@pytest.mark.parametrize("gather", ["0", "1"])
 @pytest.mark.parametrize("name", ["suze_odd_101x67_5spp_2b", "default_64x64_16spp_4b", "ultracomplex_160x90_16spp_4b"])
-def test_tile_split_is_bit_identical(rtc, name):
+def test_tile_split_is_bit_identical(rtc, name, gather, monkeypatch):
+    """Both ways of assembling the frame: every device copies its own bands to the host image (default), or NCCL
+    all-gather + un-interleave on device 0 and one copy (RTC_GATHER=1)."""
+    monkeypatch.setenv("RTC_GATHER", gather)
     e = util.kat()[name]
     job = util.job_of(e)
     tris = util.scene_tris(e["scene"])
