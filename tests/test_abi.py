@@ -101,6 +101,18 @@ def test_argument_checks(rtc):
         assert e.value.code == 1, kw  # RTC_ERR_ARG comes before any device work
 
 
+def test_download_bands_argument_checks(rtc):
+    """rtc_download_bands rejects bad arguments before any device work (no GPU needed)."""
+    from raytracingc_b200 import api
+    buf = np.zeros(64, np.uint8)
+    p = buf.ctypes.data
+    for args in ((0, 0, p, 24, 8, 2, 8, 0), (0, p, 0, 24, 8, 2, 8, 0), (0, p, p, 0, 8, 2, 8, 0), (0, p, p, 24, 0, 2, 8, 0),
+                 (0, p, p, 24, 8, 0, 8, 0), (0, p, p, 24, 8, 2, 0, 0), (0, p, p, 24, 8, 2, 8, 2), (0, p, p, 24, 8, 2, 8, -1)):
+        with pytest.raises(rtc.RtcError) as e:
+            api.download_bands(*args)
+        assert e.value.code == 1, args
+
+
 def test_product_never_imports_the_oracle():
     """oracle/ is test infrastructure: nothing under raytracingc_b200/ or include/ may reference it"""
     for d in ("raytracingc_b200", "include"):
