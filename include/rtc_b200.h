@@ -52,6 +52,9 @@ extern "C" {
                                    fallback for scenes whose stored normals do not follow the winding) */
 #define RTC_FLAG_PATHS_ONLY 4u  /* no primary pre-filter: every pixel goes through the
                                    path kernel (exact arithmetic, shared-memory tiles) */
+#define RTC_FLAG_SERIAL_PATHS 128u /* path kernel, first form: one lane owns one pixel and runs its samples in
+                                      sequence (validation mode for the pool kernel, which evaluates a pixel's samples
+                                      out of order; also taken automatically when maxBounce > 255) */
 
 /* counters a caller can ask for; replaces the reference's printf progress */
 typedef struct RenderStats {
@@ -68,6 +71,10 @@ typedef struct RenderStats {
     int32_t ngpus_used;
     uint64_t check_failures; /* device self-checks, must be 0: samples whose primary re-sweep disagreed with the
                                 classification + (RTC_FLAG_VERIFY_QUICK) accepted pairs the quick test had dropped */
+    /* scheduler counters of the path kernel (pool form): samples evaluated (those consumed by a pixel + speculative
+     * ones that were dropped), shade passes, lanes they filled (of 32), sweep passes, rays they carried (of 64),
+     * scheduler iterations.  rays/tri_pairs above count consumed samples only. */
+    uint64_t pool_samples_evaluated, pool_shade_passes, pool_shade_lanes, pool_sweep_passes, pool_sweep_rays, pool_iterations;
 } RenderStats;
 
 /*
@@ -183,8 +190,10 @@ void rtc_subset_size(int32_t width, int32_t height, const RtcSubset *s, int32_t 
  *   d_stats   RTC_DEVICE_STATS_WORDS uint64 counters, ADDED to (zero them first):
  *             [0] rays [1] ray-triangle pairs [2] ray-sphere pairs [3..8] pairs by reference exit
  *             (RTC_FLAG_COUNT_EXITS) [9] primary-hit pixels (d_ids != NULL) [10] pairs sent to the exact path
+ *             [11] self-check failures (must stay 0) [12..17] path-kernel scheduler counters, in the order of
+ *             RenderStats.pool_*
  */
-#define RTC_DEVICE_STATS_WORDS 16
+#define RTC_DEVICE_STATS_WORDS 24
 int rtc_render_device(const RtcScene *scene, const Scene *sky, const Camera *cam, const RtcDeviceJob *job,
                       uint8_t *d_rgb, float *d_accum, int32_t *d_ids, uint64_t *d_stats, void *stream);
 

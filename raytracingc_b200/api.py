@@ -28,8 +28,8 @@ SPHERE_DTYPE = np.dtype(
 
 RTC_SPLIT_TILES, RTC_SPLIT_SAMPLES = 0, 1
 RTC_FLAG_COUNT_EXITS, RTC_FLAG_EXACT_ONLY, RTC_FLAG_PATHS_ONLY, RTC_FLAG_PER_PAIR_FILTER, RTC_FLAG_TIME_KERNELS = 1, 2, 4, 8, 16
-RTC_FLAG_VERIFY_QUICK, RTC_FLAG_REF_QUICK = 32, 64
-STATS_WORDS = 16
+RTC_FLAG_VERIFY_QUICK, RTC_FLAG_REF_QUICK, RTC_FLAG_SERIAL_PATHS = 32, 64, 128
+STATS_WORDS = 24
 ERRORS = {1: "RTC_ERR_ARG", 2: "RTC_ERR_NO_GPU", 3: "RTC_ERR_CUDA", 4: "RTC_ERR_NCCL", 5: "RTC_ERR_NOMEM"}
 
 # the sphere the reference hard-codes (scene.h:17-19); used when trianglesOnly == 0
@@ -53,7 +53,9 @@ class RenderStats(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("tri_pairs", C.c_uint64), ("sphere_pairs", C.c_uint64),
                 ("tri_exit", C.c_uint64 * 6), ("hit_pixels", C.c_uint64), ("upload_ms", C.c_float),
                 ("kernel_ms", C.c_float), ("gather_ms", C.c_float), ("download_ms", C.c_float),
-                ("kernels_launched", C.c_int32), ("ngpus_used", C.c_int32), ("check_failures", C.c_uint64)]
+                ("kernels_launched", C.c_int32), ("ngpus_used", C.c_int32), ("check_failures", C.c_uint64),
+                ("pool_samples_evaluated", C.c_uint64), ("pool_shade_passes", C.c_uint64), ("pool_shade_lanes", C.c_uint64),
+                ("pool_sweep_passes", C.c_uint64), ("pool_sweep_rays", C.c_uint64), ("pool_iterations", C.c_uint64)]
 
     def as_dict(self):
         return {k: (list(getattr(self, k)) if k == "tri_exit" else getattr(self, k)) for k, _ in self._fields_}

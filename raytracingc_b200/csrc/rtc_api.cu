@@ -20,6 +20,7 @@
 #include "rtc_kernels.cuh"
 #include "rtc_fast.cuh"
 #include "rtc_paths.cuh"
+#include "rtc_pool.cuh"
 #include "rtc_sky.cuh"
 #include "rtc_skyblock.cuh"
 
@@ -95,7 +96,8 @@ struct RtcScene {
     size_t cap_btask = 0;
     cudaEvent_t kev[3] = {nullptr, nullptr, nullptr}; // RTC_FLAG_TIME_KERNELS: before primary, between, after paths
     bool kev_valid = false;
-    unsigned *counters = nullptr; // [0] list length, [1] path-kernel work cursor
+    unsigned *counters = nullptr; // [0] list length, [1] path-kernel work cursor, [2] block tasks, [3] their cursor,
+                                  // [4] pool kernel: scheduler watchdog tripped
     float4 *qrec = nullptr;       // quick records of the path kernel's first phase (rtc_paths.cuh)
     int q_layout = 0;             // layout qrec currently holds: 1 per triangle, 2 per pair (packed), 0 none
     int cap_q = 0;
@@ -503,7 +505,7 @@ int ensure_scratch(RtcScene *sc, size_t npix, size_t nbtask = 0)
         sc->cap_btask = nbtask;
     }
     if (!sc->counters)
-        CU(cudaMalloc(&sc->counters, 4 * sizeof(unsigned)));
+        CU(cudaMalloc(&sc->counters, 8 * sizeof(unsigned)));
     if (npix > sc->cap_list || !sc->list) {
         CU(cudaFree(sc->list));
         sc->list = nullptr;
@@ -517,6 +519,99 @@ int ensure_scratch(RtcScene *sc, size_t npix, size_t nbtask = 0)
         CU(cudaDeviceGetAttribute(&sc->nsm, cudaDevAttrMultiProcessorCount, sc->device));
         CU(cudaDeviceGetAttribute(&sc->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, sc->device));
     }
+    return RTC_OK;
+}
+
+// quick records of the path kernels' first phase (rtc_paths.cuh), built once per scene and again only when a ray
+// origin leaves the bound they were built for or the layout changes
+int ensure_quick_records(RtcScene *sc, const rtc::RenderArgs &a, int mode, bool has_rec, cudaStream_t st)
+{
+    // bounce rays start on the scene's surfaces; only when the path kernel sweeps the primary rays too does the camera count
+    float need = sc->bound_abs;
+    if (!has_rec)
+        need = std::fmax(need, std::fmax(std::fabs(a.origin.x), std::fmax(std::fabs(a.origin.y), std::fabs(a.origin.z))));
+    need = need * 1.001f + 1e-6f;
+    if (sc->ntris > sc->cap_q || !sc->qrec) {
+        cudaFree(sc->qrec);
+        sc->qrec = nullptr;
+        // room for either layout: 4 float4 per triangle, or QPAIR_F4 per pair of triangles
+        CU(cudaMalloc(&sc->qrec, sizeof(float4) * (rtc::path_q_f4(5, sc->ntris) + rtc::QPAIR_F4)));
+        sc->cap_q = sc->ntris > 0 ? sc->ntris : 1;
+        sc->q_obound = 0.f;
+    }
+    const int q_layout = rtc::mode_layout(mode);
+    if ((!(need <= sc->q_obound) || sc->q_layout != q_layout) && sc->ntris > 0) {
+        const float ob = sc->q_layout != q_layout && need <= sc->q_obound ? sc->q_obound : need * 1.25f;
+        rtc::quick_records_kernel<<<(sc->ntris + 127) / 128, 128, 0, st>>>(sc->geo, sc->ntris, ob, sc->qrec, q_layout);
+        CU(cudaGetLastError());
+        sc->q_obound = ob;
+        sc->q_layout = q_layout;
+    }
+    return RTC_OK;
+}
+
+// The path kernel, pool form (rtc_pool.cuh): the default for every frame it supports.
+int launch_pool(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const float2 *rec, int planes, int write_ids,
+                int mode, cudaStream_t st)
+{
+    rtc::PoolWork w;
+    memset(&w, 0, sizeof w);
+    if (mode != 0) {
+        int rc_q = ensure_quick_records(sc, a, mode, rec != nullptr, st);
+        if (rc_q)
+            return rc_q;
+        w.qrec = sc->qrec;
+        w.obound = sc->q_obound;
+    }
+    w.list = list;
+    w.rec = rec;
+    w.list_count = sc->counters;
+    w.cursor = sc->counters + 1;
+    w.error = sc->counters + 4;
+    w.planes = planes;
+    w.write_ids = write_ids;
+    w.spec = env_int("RTC_NO_SPEC", 0) == 0;
+    w.ctx_share_div = std::max(1, env_int("RTC_POOL_SHARE_DIV", 2));
+    w.tile = env_int("RTC_PATH_TILE", rtc::PATH_TILE);
+    if (w.tile < 1 || w.tile > rtc::PATH_TILE)
+        w.tile = rtc::PATH_TILE;
+    if (rtc::mode_packed(mode) && (w.tile & 1))
+        w.tile += 1; // pair records: a tile starts on an even triangle (PATH_TILE is even)
+    // configuration by the size of the resident scene: two 8-warp CTAs per SM, one 16-warp CTA, or streamed tiles
+    const size_t budget = (size_t)sc->max_smem_optin; // per CTA; an SM holds this + 1 KB per CTA as well
+    const size_t res8 = rtc::pool_smem_bytes(sc->ntris, false, mode, rtc::POOL_WARPS_SMALL);
+    const size_t res16 = rtc::pool_smem_bytes(sc->ntris, false, mode, rtc::POOL_WARPS_LARGE);
+    int cfg = res8 * 2 + 2048 <= budget ? 0 : (res16 <= budget ? 1 : 2);
+    const int force = env_int("RTC_POOL_CFG", -1);
+    if (env_int("RTC_FORCE_STREAM", 0) != 0)
+        cfg = 2;
+    else if (force >= cfg && force <= 2)
+        cfg = force; // a larger configuration than needed (tests, A/B)
+    const int warps = cfg == 0 ? rtc::POOL_WARPS_SMALL : rtc::POOL_WARPS_LARGE;
+    const size_t smem = rtc::pool_smem_bytes(sc->ntris, cfg == 2, mode, warps);
+    using PoolKernel = void (*)(const rtc::RenderArgs, const rtc::PoolWork);
+    // [cfg][mode slot]: mode 0 (reference arithmetic), 3 (packed quick records), 4 (3 + verification)
+#define RTC_POOL_ROW(S_, W_) \
+    {rtc::render_pool_kernel<S_, 0, W_>, rtc::render_pool_kernel<S_, 3, W_>, rtc::render_pool_kernel<S_, 4, W_>}
+    static const PoolKernel kernels[3][3] = {RTC_POOL_ROW(false, rtc::POOL_WARPS_SMALL), RTC_POOL_ROW(false, rtc::POOL_WARPS_LARGE),
+                                             RTC_POOL_ROW(true, rtc::POOL_WARPS_LARGE)};
+#undef RTC_POOL_ROW
+    const PoolKernel kern = kernels[cfg][mode == 0 ? 0 : (mode == 3 ? 1 : 2)];
+    int per_sm = 0;
+    int rc_o = kernel_occupancy(sc->device, reinterpret_cast<const void *>(kern), 32 * warps, smem, &per_sm);
+    if (rc_o)
+        return rc_o;
+    if (per_sm < 1)
+        return fail(RTC_ERR_CUDA, "pool kernel does not fit on an SM (smem %zu)", smem);
+    const long long tasks = (long long)a.out_w * a.out_h * planes; // upper bound when a list is used
+    const long long want = (tasks + warps - 1) / warps;           // at least one pixel per warp
+    const int blocks = (int)std::min<long long>((long long)sc->nsm * per_sm, want > 0 ? want : 1);
+    // a scheduler iteration runs a pass or hands out work; far more of them than a warp could ever need means a bug:
+    // the kernel then stops and reports instead of hanging the device
+    const double bound = (double)tasks * (double)a.spp * (2.0 * a.maxBounce + 4.0) + 1e4;
+    w.watchdog = (unsigned long long)std::min(bound, 4e7);
+    kern<<<blocks, 32 * warps, smem, st>>>(a, w);
+    CU(cudaGetLastError());
     return RTC_OK;
 }
 
@@ -536,30 +631,17 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
     const int mode = ref_quick ? 0 : ((flags & RTC_FLAG_VERIFY_QUICK) ? form + 1 : (sc->quick_ok ? form : 0));
     if (rtc::mode_verify(mode) && !a.stats)
         return fail(RTC_ERR_ARG, "RTC_FLAG_VERIFY_QUICK needs a stats buffer");
+    // the pool kernel (samples out of order, two rays per lane) unless the first form is asked for, the quick records
+    // are wanted one triangle at a time (RTC_QUICK_FORM=1), or a path can be longer than its 8-bit counters
+    if (!(flags & RTC_FLAG_SERIAL_PATHS) && env_int("RTC_PATHS_V1", 0) == 0 && a.maxBounce <= rtc::POOL_MAX_BOUNCE &&
+        (mode == 0 || mode == 3 || mode == 4))
+        return launch_pool(sc, a, list, rec, planes, write_ids, mode, st);
     w.qrec = nullptr;
     w.obound = 0.f;
     if (mode != 0) {
-        // bounce rays start on the scene's surfaces; only when this kernel sweeps the primary rays too does the camera count
-        float need = sc->bound_abs;
-        if (!rec)
-            need = std::fmax(need, std::fmax(std::fabs(a.origin.x), std::fmax(std::fabs(a.origin.y), std::fabs(a.origin.z))));
-        need = need * 1.001f + 1e-6f;
-        if (sc->ntris > sc->cap_q || !sc->qrec) {
-            cudaFree(sc->qrec);
-            sc->qrec = nullptr;
-            // room for either layout: 4 float4 per triangle, or QPAIR_F4 per pair of triangles
-            CU(cudaMalloc(&sc->qrec, sizeof(float4) * (rtc::path_q_f4(5, sc->ntris) + rtc::QPAIR_F4)));
-            sc->cap_q = sc->ntris > 0 ? sc->ntris : 1;
-            sc->q_obound = 0.f;
-        }
-        const int q_layout = rtc::mode_layout(mode);
-        if ((!(need <= sc->q_obound) || sc->q_layout != q_layout) && sc->ntris > 0) {
-            const float ob = sc->q_layout != q_layout && need <= sc->q_obound ? sc->q_obound : need * 1.25f;
-            rtc::quick_records_kernel<<<(sc->ntris + 127) / 128, 128, 0, st>>>(sc->geo, sc->ntris, ob, sc->qrec, q_layout);
-            CU(cudaGetLastError());
-            sc->q_obound = ob;
-            sc->q_layout = q_layout;
-        }
+        int rc_q = ensure_quick_records(sc, a, mode, rec != nullptr, st);
+        if (rc_q)
+            return rc_q;
         w.qrec = sc->qrec;
         w.obound = sc->q_obound;
     }
@@ -736,7 +818,7 @@ static int render_device_impl(const RtcScene *sc, const Scene *sky, const Camera
                                (size_t)((job->out_h + rtc::BLK_H - 1) / rtc::BLK_H + 16) * (size_t)planes;
         if ((rc = ensure_scratch(msc, (size_t)job->out_w * job->out_h, nblocks)))
             return rc;
-        CU(cudaMemsetAsync(msc->counters, 0, 4 * sizeof(unsigned), st));
+        CU(cudaMemsetAsync(msc->counters, 0, 8 * sizeof(unsigned), st));
     }
     const bool timed = (job->flags & RTC_FLAG_TIME_KERNELS) != 0 && R > 0;
     msc->kev_valid = false;
@@ -1343,6 +1425,9 @@ int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const
             }
         }
     }
+    if (tot[rtc::ST_MISMATCH] >> 40)
+        return fail(RTC_ERR_CUDA, "path kernel: scheduler watchdog tripped (%llu warp(s)); the image is incomplete",
+                    tot[rtc::ST_MISMATCH] >> 40);
     if (p->stats) {
         RenderStats *st = p->stats;
         memset(st, 0, sizeof *st);
@@ -1353,6 +1438,12 @@ int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const
             st->tri_exit[e] = tot[rtc::ST_EXIT0 + e];
         st->hit_pixels = tot[rtc::ST_HIT_PIXELS];
         st->check_failures = tot[rtc::ST_MISMATCH];
+        st->pool_samples_evaluated = tot[rtc::ST_POOL_EVAL];
+        st->pool_shade_passes = tot[rtc::ST_POOL_SHADE_PASSES];
+        st->pool_shade_lanes = tot[rtc::ST_POOL_SHADE_LANES];
+        st->pool_sweep_passes = tot[rtc::ST_POOL_SWEEP_PASSES];
+        st->pool_sweep_rays = tot[rtc::ST_POOL_SWEEP_RAYS];
+        st->pool_iterations = tot[rtc::ST_POOL_ITERS];
         st->upload_ms = up_ms;
         st->kernel_ms = k_ms;
         float gms = 0;

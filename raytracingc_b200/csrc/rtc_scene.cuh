@@ -51,9 +51,27 @@ struct RenderArgs {
     // [2K..3K) = flags set to 1 when a chunk's pixels are all final.  null: not tracked.
     unsigned *prog;
     int prog_rows, prog_chunks;
+    // 1: rgb is the FULL image (W x H, possibly a peer device's memory): a pixel is stored at its final row and column
+    // instead of its compact position -- the ranks of a tile split write straight into the destination frame.
+    int rgb_full;
 };
 
+// byte offset of compact pixel `pix` (cj * out_w + ci) in a.rgb
+__device__ __forceinline__ size_t pixel_offset(const RenderArgs &a, int pix)
+{
+    if (!a.rgb_full)
+        return (size_t)pix * 3;
+    const int ci = pix % a.out_w, cj = pix / a.out_w;
+    const int x = a.col_start + ci * a.col_step;
+    const int y = a.row_start + (cj / a.band_h) * a.row_step + (cj % a.band_h);
+    return ((size_t)y * a.W + x) * 3;
+}
+
 // stats words
-enum { ST_RAYS = 0, ST_TRI_PAIRS = 1, ST_SPH_PAIRS = 2, ST_EXIT0 = 3, /* ..8 */ ST_HIT_PIXELS = 9, ST_SLOW_PAIRS = 10, ST_MISMATCH = 11 };
+enum { ST_RAYS = 0, ST_TRI_PAIRS = 1, ST_SPH_PAIRS = 2, ST_EXIT0 = 3, /* ..8 */ ST_HIT_PIXELS = 9, ST_SLOW_PAIRS = 10, ST_MISMATCH = 11,
+       // scheduler counters of the pool kernel (rtc_pool.cuh): samples evaluated (consumed ones + dropped speculative
+       // ones), shade passes and the lanes they filled, sweep passes and the rays they carried, scheduler iterations
+       ST_POOL_EVAL = 12, ST_POOL_SHADE_PASSES = 13, ST_POOL_SHADE_LANES = 14, ST_POOL_SWEEP_PASSES = 15,
+       ST_POOL_SWEEP_RAYS = 16, ST_POOL_ITERS = 17 };
 
 } // namespace rtc

@@ -32,7 +32,7 @@ def _gpu_lattice(tris, job, flags=0, nsplit=1, ngpus=1, split_mode=0):
     dev = torch.device("cuda", 0)
     rgb = torch.zeros((dj.out_h, dj.out_w, 3), dtype=torch.uint8, device=dev)
     ids = torch.full((dj.out_h, dj.out_w), -7, dtype=torch.int32, device=dev)
-    stats = torch.zeros(16, dtype=torch.int64, device=dev)
+    stats = torch.zeros(24, dtype=torch.int64, device=dev)
     acc = torch.zeros((max(nsplit, 1), dj.out_h, dj.out_w, 3), dtype=torch.float32, device=dev)
     cam, sky = rtc.camera_look_at(job.origin, job.look_at, job.fov), rtc.make_scene()
     st = torch.cuda.current_stream().cuda_stream

@@ -28,7 +28,7 @@ job.to_c()
 dev = torch.device("cuda", 0)
 rgb = torch.zeros((job.out_h, job.out_w, 3), dtype=torch.uint8, device=dev)
 acc = torch.zeros((max(a.nsplit, 1), job.out_h, job.out_w, 3), dtype=torch.float32, device=dev)
-stats = torch.zeros(16, dtype=torch.int64, device=dev)
+stats = torch.zeros(24, dtype=torch.int64, device=dev)
 cam, sky = rtc.camera_look_at(), rtc.make_scene()
 st = torch.cuda.current_stream()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -27,7 +27,7 @@ job = rtc.DeviceJob(W, H, spp, bounce, triangles_only=tonly, subset=split.band_s
 job.to_c()
 dev = torch.device("cuda", 0)
 rgb = torch.zeros((job.out_h, job.out_w, 3), dtype=torch.uint8, device=dev)
-stats = torch.zeros(16, dtype=torch.int64, device=dev)
+stats = torch.zeros(24, dtype=torch.int64, device=dev)
 cam, sky = rtc.camera_look_at(), rtc.make_scene()
 st = torch.cuda.current_stream()
 for i in range(a.frames):
@@ -40,4 +40,6 @@ for i in range(a.frames):
     pm, qm = sc.kernel_times()
     s = stats.cpu().numpy()
     print(f"rank {a.rank}/{a.gpus} frame {i}: {e0.elapsed_time(e1):.3f} ms (primary {pm:.3f}, paths {qm:.3f}), rays {int(s[0])}, "
-          f"hit pixels {int(s[9])}, check failures {int(s[11])}")
+          f"hit pixels {int(s[9])}, check failures {int(s[11])}; pool: samples evaluated {int(s[12])}, shade passes {int(s[13])} "
+          f"({int(s[14]) / max(int(s[13]), 1):.1f} lanes), sweep passes {int(s[15])} ({int(s[16]) / max(int(s[15]), 1):.1f} rays), "
+          f"iterations {int(s[17])}")
