@@ -55,6 +55,16 @@ def build_lib(force: bool = False, verbose: bool = False) -> str:
     return LIB
 
 
+def build_variant(name: str, defines: list[str], verbose: bool = False) -> str:
+    """An alternative build of the library with extra -D flags (A/B measurements: run with RTC_B200_LIB=<path>)."""
+    out = os.path.join(PKG, f"librtc_b200_{name}.so")
+    cmd = [_nvcc(), *NVCC_FLAGS, *[f"-D{d}" for d in defines], "-o", out, os.path.join(CSRC, "rtc_api.cu"), "-ldl"]
+    if verbose:
+        cmd += ["-Xptxas", "-v"]
+    subprocess.run(cmd, check=True)
+    return out
+
+
 def build_host(force: bool = False) -> str | None:
     """The host C program (CLI + OBJ loader + image writer) that links librtc_b200.so."""
     mk = os.path.join(HOST_DIR, "Makefile")

@@ -551,8 +551,8 @@ int ensure_quick_records(RtcScene *sc, const rtc::RenderArgs &a, int mode, bool 
 }
 
 // The path kernel, pool form (rtc_pool.cuh): the default for every frame it supports.
-int launch_pool(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const float2 *rec, int planes, int write_ids,
-                int mode, cudaStream_t st)
+int launch_pool(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const float2 *rec, int planes, int mode,
+                cudaStream_t st)
 {
     rtc::PoolWork w;
     memset(&w, 0, sizeof w);
@@ -569,7 +569,6 @@ int launch_pool(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const f
     w.cursor = sc->counters + 1;
     w.error = sc->counters + 4;
     w.planes = planes;
-    w.write_ids = write_ids;
     w.spec = env_int("RTC_NO_SPEC", 0) == 0;
     w.ctx_share_div = std::max(1, env_int("RTC_POOL_SHARE_DIV", 2));
     w.tile = env_int("RTC_PATH_TILE", rtc::PATH_TILE);
@@ -581,7 +580,8 @@ int launch_pool(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const f
     const size_t budget = (size_t)sc->max_smem_optin; // per CTA; an SM holds this + 1 KB per CTA as well
     const size_t res8 = rtc::pool_smem_bytes(sc->ntris, false, mode, rtc::POOL_WARPS_SMALL);
     const size_t res16 = rtc::pool_smem_bytes(sc->ntris, false, mode, rtc::POOL_WARPS_LARGE);
-    int cfg = res8 * 2 + 2048 <= budget ? 0 : (res16 <= budget ? 1 : 2);
+    const size_t sm_total = budget + 1024; // an SM's shared memory; every resident CTA also reserves 1 KB of it
+    int cfg = (res8 + 1024) * rtc::POOL_MINB_SMALL <= sm_total ? 0 : (res16 <= budget ? 1 : 2);
     const int force = env_int("RTC_POOL_CFG", -1);
     if (env_int("RTC_FORCE_STREAM", 0) != 0)
         cfg = 2;
@@ -631,11 +631,12 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
     const int mode = ref_quick ? 0 : ((flags & RTC_FLAG_VERIFY_QUICK) ? form + 1 : (sc->quick_ok ? form : 0));
     if (rtc::mode_verify(mode) && !a.stats)
         return fail(RTC_ERR_ARG, "RTC_FLAG_VERIFY_QUICK needs a stats buffer");
-    // the pool kernel (samples out of order, two rays per lane) unless the first form is asked for, the quick records
-    // are wanted one triangle at a time (RTC_QUICK_FORM=1), or a path can be longer than its 8-bit counters
-    if (!(flags & RTC_FLAG_SERIAL_PATHS) && env_int("RTC_PATHS_V1", 0) == 0 && a.maxBounce <= rtc::POOL_MAX_BOUNCE &&
-        (mode == 0 || mode == 3 || mode == 4))
-        return launch_pool(sc, a, list, rec, planes, write_ids, mode, st);
+    // the pool kernel (samples out of order, two rays per lane) for the pixels whose primary hit is known, unless the
+    // first form is asked for, the quick records are wanted one triangle at a time (RTC_QUICK_FORM=1), or a path can be
+    // longer than its 8-bit counters
+    if (list != nullptr && rec != nullptr && !(flags & RTC_FLAG_SERIAL_PATHS) && env_int("RTC_PATHS_V1", 0) == 0 &&
+        a.maxBounce <= rtc::POOL_MAX_BOUNCE && (mode == 0 || mode == 3 || mode == 4))
+        return launch_pool(sc, a, list, rec, planes, mode, st);
     w.qrec = nullptr;
     w.obound = 0.f;
     if (mode != 0) {

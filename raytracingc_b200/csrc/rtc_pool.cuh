@@ -14,11 +14,11 @@
 // HOW: a warp owns a pool in shared memory: POOL_NS evaluation slots (one path each: ray, throughput, light, RNG
 // state, offset) and POOL_NC pixel contexts (accumulator, walk pointer j, next unassigned offset, primary ray + hit).
 // The warp alternates between
-//     consume   finished slots are consumed by their pixel in offset order (acc += light, j += h); slots whose offset
-//               was skipped are freed; a pixel whose last sample is consumed is written
-//     refill    new pixels from the global work list while the warp holds fewer than its share; every context with
-//               nothing outstanding gets a slot (that alone is the serial stream of the reference); slots left over
-//               become speculative children at the next unassigned offsets of the contexts that can still use them
+//     consume   lane c walks its pixel context: finished slots are consumed in offset order (acc += light, j += h), the
+//               slots of skipped offsets are freed, a pixel whose last sample is consumed is written
+//     refill    idle contexts take new pixels from the global work list (at most the warp's share at a time); every
+//               context with nothing outstanding gets a slot (that alone is the serial stream of the reference); slots
+//               left over become speculative children at the next unassigned offsets of the contexts that can use them
 //     shade     up to 32 slots whose ray hit something: calcColor's loop body (raytracing.c:272-287), one per lane
 //     sweep     up to 64 slots with a ray to trace: closest hit over ALL triangles (calculateRayCollision,
 //               raytracing.c:216-240), TWO rays per lane sharing every warp-uniform record load; misses are shaded
@@ -38,31 +38,37 @@ namespace rtc {
 #ifndef RTC_POOL_NS
 #define RTC_POOL_NS 96
 #endif
-#ifndef RTC_POOL_NC
-#define RTC_POOL_NC 64
+// Warps per CTA and CTAs per SM of the resident form (A/B knobs); one CTA of POOL_WARPS_LARGE warps per SM when the
+// scene is large or streamed (the tiles' double buffer is then shared by more warps).
+#ifndef RTC_POOL_WARPS_SMALL
+#define RTC_POOL_WARPS_SMALL 8
 #endif
-// Warps per CTA: 8 (two CTAs per SM) while the resident scene leaves room for two sets of pools, else 16 (one CTA per SM;
-// always when the scene is streamed: the tiles' double buffer is shared by more warps).  16 warps x 96 slots per SM either way.
-constexpr int POOL_WARPS_SMALL = 8, POOL_WARPS_LARGE = 16;
-constexpr int POOL_NS = RTC_POOL_NS; // evaluation slots per warp (multiple of 32, <= 96 + 32 * k is fine)
-constexpr int POOL_NC = RTC_POOL_NC; // pixel contexts per warp (multiple of 32, <= 256: the context index has 8 bits)
-constexpr int POOL_SPL = POOL_NS / 32, POOL_CPL = POOL_NC / 32; // slots / contexts owned per lane
-static_assert(POOL_NS % 32 == 0 && POOL_NC % 32 == 0 && POOL_NC <= 256 && POOL_NS <= 255, "pool geometry");
+#ifndef RTC_POOL_MINB_SMALL
+#define RTC_POOL_MINB_SMALL 2
+#endif
+#ifndef RTC_POOL_UP // pair records per iteration of the two-ray quick test
+#define RTC_POOL_UP 1
+#endif
+constexpr int POOL_WARPS_SMALL = RTC_POOL_WARPS_SMALL, POOL_WARPS_LARGE = 16, POOL_MINB_SMALL = RTC_POOL_MINB_SMALL;
+constexpr int POOL_NS = RTC_POOL_NS; // evaluation slots per warp (multiple of 32)
+constexpr int POOL_NC = 32;          // pixel contexts per warp: context c belongs to lane c
+constexpr int POOL_SPL = (POOL_NS + 31) / 32; // slots a lane looks after (lane, lane + 32, ...; the last row may be cut)
+#ifndef RTC_POOL_RING
+#define RTC_POOL_RING 32
+#endif
+constexpr int POOL_RING = RTC_POOL_RING; // outstanding offsets per context (a power of two)
+static_assert(POOL_NS % 4 == 0 && POOL_NS >= 64 && POOL_NS <= 224 && (POOL_RING & (POOL_RING - 1)) == 0, "pool geometry");
 constexpr int POOL_MAX_BOUNCE = 255; // bounce and hit counters are 8-bit fields of the slot's meta word
 
 // slot fields (one array of POOL_NS words each)
-enum { E_PX, E_PY, E_PZ, E_DX, E_DY, E_DZ, E_TX, E_TY, E_TZ, E_LX, E_LY, E_LZ, E_RNG, E_BEST, E_ID, E_OFF, E_META, E_FIELDS };
+enum { E_PX, E_PY, E_PZ, E_DX, E_DY, E_DZ, E_TX, E_TY, E_TZ, E_LX, E_LY, E_LZ, E_RNG, E_BEST, E_ID, E_META, E_FIELDS };
 // context fields (one array of POOL_NC words each)
 enum { C_PIX, C_PLANE, C_REM, C_TOTAL, C_J, C_TOP, C_TSTATE, C_AX, C_AY, C_AZ, C_DX, C_DY, C_DZ, C_BEST0, C_ID0, C_FIELDS };
-constexpr int POOL_WORDS = E_FIELDS * POOL_NS + C_FIELDS * POOL_NC + (2 * POOL_NS + POOL_NC + 3) / 4 + 1;
+constexpr int POOL_WORDS = E_FIELDS * POOL_NS + C_FIELDS * POOL_NC + (POOL_NC * POOL_RING + 2 * POOL_NS) / 4;
 
-// meta word of a slot: [1:0] state, [2] first sweep of the pixel (ids), [10:3] context, [18:11] bounce, [26:19] hits
+// meta word of a slot: [1:0] state, [18:11] bounce, [26:19] hits
 enum { SL_FREE = 0, SL_SHADE = 1, SL_SWEEP = 2, SL_DONE = 3 };
-constexpr unsigned SL_FIRST = 4u;
-__device__ __forceinline__ unsigned meta_make(unsigned st, unsigned ctx, unsigned bounce, unsigned hits, unsigned first = 0)
-{
-    return st | first | (ctx << 3) | (bounce << 11) | (hits << 19);
-}
+__device__ __forceinline__ unsigned meta_make(unsigned st, unsigned bounce, unsigned hits) { return st | (bounce << 11) | (hits << 19); }
 
 // 7 steps of the LCG of moremath.c:91 as one multiply-add
 __host__ __device__ constexpr uint32_t lcg_mul(int steps)
@@ -82,15 +88,14 @@ __host__ __device__ constexpr uint32_t lcg_add(int steps)
 constexpr uint32_t LCG7_M = lcg_mul(7), LCG7_C = lcg_add(7);
 
 struct PoolWork {
-    const int *list;            // compact pixel indices of the primary-hit pixels, or nullptr = every pixel
-    const unsigned *list_count; // device counter written by the primary kernel (used when list != nullptr)
-    const float2 *rec;          // {distance, id bits} of each listed pixel's primary hit; nullptr: this kernel sweeps primary rays
+    const int *list;            // compact pixel indices of the primary-hit pixels
+    const unsigned *list_count; // device counter written by the primary kernel
+    const float2 *rec;          // {distance, id bits} of each listed pixel's primary hit
     unsigned *cursor;           // device work cursor, zeroed before the launch
     unsigned *error;            // set to 1 when a warp's scheduler trips its watchdog (a bug: never in a correct build)
     int planes;                 // sub-streams rendered by this launch
-    int write_ids;              // 1: this kernel owns the primary-id map (no primary kernel ran)
     int tile;                   // triangles per streamed tile (<= PATH_TILE), STREAM only
-    int spec;                   // 1: speculative children allowed (needs rec)
+    int spec;                   // 1: speculative children allowed
     int ctx_share_div;          // a warp holds at most ceil(tasks / (warps * div)) pixels at a time (>= 1, <= POOL_NC)
     const float4 *qrec;         // MODE >= 1: quick records
     float obound;
@@ -102,78 +107,68 @@ __host__ __device__ inline size_t pool_smem_bytes(int ntris, bool stream, int mo
     return path_smem_bytes(ntris, stream, mode) + (size_t)warps * POOL_WORDS * sizeof(uint32_t);
 }
 
-// ---- the sweep of NR rays per lane over one resident scene / one streamed tile -------------------------------
+// ---- the sweep of TWO rays per lane over one resident scene / one streamed tile -------------------------------
 // Same two phases as sweep_chunked (rtc_paths.cuh): branch-free conservative quick test of every pair, then the
-// reference's exact sequence on the survivors in index order.  With NR = 2 every warp-uniform LDS.128 of a pair
-// record feeds both rays (a uniform LDS.128 costs two shared-memory wavefronts whatever it carries: the pipe that
-// bounds the one-ray form).
-template <int MODE, int NR, int UNROLL>
-__device__ __forceinline__ void sweep_multi(const float4 *S, const float4 *geo, float obound, int n, int base,
-                                            const bool (&act)[NR], const f3 (&o)[NR], const f3 (&d)[NR], float (&best)[NR],
-                                            int (&bestId)[NR], unsigned &viol)
+// reference's exact sequence on the survivors in index order.  Every warp-uniform LDS.128 of a pair record feeds both
+// rays (a uniform LDS.128 costs two shared-memory wavefronts whatever it carries: the pipe that bounds the one-ray
+// form).  The loops are kept small on purpose: the SM's L0 instruction cache holds ~6 KB and the
+// warps of an SM sub-partition are in different phases of this kernel.
+template <int MODE>
+__device__ __forceinline__ void sweep_two(const float4 *S, const float4 *geo, float obound, int n, int base, const bool (&act)[2],
+                                          const f3 (&o)[2], const f3 (&d)[2], float (&best)[2], int (&bestId)[2], unsigned &viol)
 {
-    bool rayok[NR];
-    QuickRay2 q2[NR];
+    bool rayok[2];
+    QuickRay2 q2[2];
 #pragma unroll
-    for (int r = 0; r < NR; ++r) {
+    for (int r = 0; r < 2; ++r) {
         rayok[r] = MODE == 0 || quick_ray_ok(o[r], d[r], obound);
         q2[r] = quick_ray2(quick_ray(o[r], d[r]));
     }
+#pragma unroll 1
     for (int c0 = 0; c0 < n; c0 += 32) {
         const int cn = min(32, n - c0);
         const unsigned full = cn == 32 ? 0xffffffffu : (1u << cn) - 1u;
-        unsigned m[NR];
-#pragma unroll
-        for (int r = 0; r < NR; ++r)
-            m[r] = 0;
+        unsigned m[2] = {0u, 0u};
         if (MODE == 0) {
-            int j = 0;
 #pragma unroll 1
-            for (; j + 2 <= cn; j += 2) {
+            for (int j = 0; j < cn; ++j) {
                 const int t0 = 3 * (c0 + j);
 #pragma unroll
-                for (int r = 0; r < NR; ++r) {
-                    unsigned m2 = 0;
-                    tri_quick_bit<1u>(o[r], d[r], S[t0], S[t0 + 1], S[t0 + 2], m2);
-                    tri_quick_bit<2u>(o[r], d[r], S[t0 + 3], S[t0 + 4], S[t0 + 5], m2);
-                    m[r] |= m2 << j;
-                }
-            }
-            for (; j < cn; ++j) {
-#pragma unroll
-                for (int r = 0; r < NR; ++r) {
+                for (int r = 0; r < 2; ++r) {
                     unsigned m1 = 0;
-                    tri_quick_bit<1u>(o[r], d[r], S[3 * (c0 + j)], S[3 * (c0 + j) + 1], S[3 * (c0 + j) + 2], m1);
+                    tri_quick_bit<1u>(o[r], d[r], S[t0], S[t0 + 1], S[t0 + 2], m1);
                     m[r] |= m1 << j;
                 }
             }
         } else {
             static_assert(MODE == 0 || mode_packed(MODE), "the pool kernel evaluates quick records in packed form");
-            constexpr int UP = UNROLL >= 2 ? UNROLL / 2 : 1; // pair records per iteration
+            constexpr int UP = RTC_POOL_UP; // pair records per iteration
             const float4 *P = S + QPAIR_F4 * (c0 >> 1);
             const int np = (cn + 1) >> 1;
             int j = 0;
 #pragma unroll 1
             for (; j + UP <= np; j += UP) {
 #pragma unroll
-                for (int r = 0; r < NR; ++r) {
+                for (int r = 0; r < 2; ++r) {
                     unsigned mg = 0;
                     quick2_pairs<0, UP>(q2[r], P + QPAIR_F4 * j, mg);
                     m[r] |= mg << (2 * j);
                 }
             }
+            if (UP > 1) {
 #pragma unroll 1
-            for (; j < np; ++j) {
+                for (; j < np; ++j) {
 #pragma unroll
-                for (int r = 0; r < NR; ++r) {
-                    unsigned m1 = 0;
-                    quick2_pairs<0, 1>(q2[r], P + QPAIR_F4 * j, m1);
-                    m[r] |= m1 << (2 * j);
+                    for (int r = 0; r < 2; ++r) {
+                        unsigned m1 = 0;
+                        quick2_pairs<0, 1>(q2[r], P + QPAIR_F4 * j, m1);
+                        m[r] |= m1 << (2 * j);
+                    }
                 }
             }
         }
 #pragma unroll
-        for (int r = 0; r < NR; ++r) {
+        for (int r = 0; r < 2; ++r) {
             m[r] &= full; // an odd count's last pair is completed by a record that never survives
             if (!rayok[r])
                 m[r] = full;
@@ -181,28 +176,38 @@ __device__ __forceinline__ void sweep_multi(const float4 *S, const float4 *geo, 
                 m[r] = 0;
         }
         const float4 *G = MODE == 0 ? S : geo;
-        if (mode_verify(MODE)) {
-#pragma unroll
-            for (int r = 0; r < NR; ++r)
-                if (act[r])
-                    for (int j = 0; j < cn; ++j) {
-                        const int i = c0 + j;
-                        unsigned ex[6] = {0, 0, 0, 0, 0, 0};
-                        float b_ = 999999.0f;
-                        int id_ = -1;
-                        tri_test_exact<true>(o[r], d[r], G[3 * i], G[3 * i + 1], G[3 * i + 2], base + i, b_, id_, ex);
-                        if (ex[5] && !((m[r] >> j) & 1u))
-                            viol++;
-                    }
-        }
-#pragma unroll
-        for (int r = 0; r < NR; ++r) {
-            unsigned mm = m[r];
+        // phase 2, ONE copy of the exact sequence for both rays (selects, no dynamically indexed registers)
+#pragma unroll 1
+        for (int r = 0; r < 2; ++r) {
+            unsigned mm = r ? m[1] : m[0];
+            if (mode_verify(MODE))
+                mm = act[r ? 1 : 0] ? full : 0u;
+            if (mm == 0u)
+                continue;
+            const unsigned quick = r ? m[1] : m[0];
+            const f3 oo = r ? o[1] : o[0], dd = r ? d[1] : d[0];
+            float b = r ? best[1] : best[0];
+            int bi = r ? bestId[1] : bestId[0];
             while (mm) {
-                const int i = c0 + __ffs(mm) - 1;
+                const int jj = __ffs(mm) - 1;
+                const int i = c0 + jj;
                 mm &= mm - 1;
-                unsigned dummy[1];
-                tri_test_exact<false>(o[r], d[r], G[3 * i], G[3 * i + 1], G[3 * i + 2], base + i, best[r], bestId[r], dummy);
+                if (mode_verify(MODE)) { // every pair runs the exact test: an accepted pair the quick test dropped is counted
+                    unsigned ex[6] = {0, 0, 0, 0, 0, 0};
+                    tri_test_exact<true>(oo, dd, G[3 * i], G[3 * i + 1], G[3 * i + 2], base + i, b, bi, ex);
+                    if (ex[5] && !((quick >> jj) & 1u))
+                        viol++;
+                } else {
+                    unsigned dummy[1];
+                    tri_test_exact<false>(oo, dd, G[3 * i], G[3 * i + 1], G[3 * i + 2], base + i, b, bi, dummy);
+                }
+            }
+            if (r) {
+                best[1] = b;
+                bestId[1] = bi;
+            } else {
+                best[0] = b;
+                bestId[0] = bi;
             }
         }
     }
@@ -210,7 +215,7 @@ __device__ __forceinline__ void sweep_multi(const float4 *S, const float4 *geo, 
 
 // ---- the kernel ---------------------------------------------------------------------------------------------
 template <bool STREAM, int MODE, int WARPS>
-__global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? 2 : 1) render_pool_kernel(const RenderArgs a, const PoolWork w)
+__global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? POOL_MINB_SMALL : 1) render_pool_kernel(const RenderArgs a, const PoolWork w)
 {
     constexpr int POOL_THREADS = 32 * WARPS;
     extern __shared__ float4 sGeo[];
@@ -231,13 +236,14 @@ __global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? 2 : 1)
     uint32_t *Eu = pool;
     float *Cf = reinterpret_cast<float *>(pool + E_FIELDS * POOL_NS);
     uint32_t *Cu = pool + E_FIELDS * POOL_NS;
-    unsigned char *freelist = reinterpret_cast<unsigned char *>(pool + E_FIELDS * POOL_NS + C_FIELDS * POOL_NC);
+    unsigned char *ring = reinterpret_cast<unsigned char *>(pool + E_FIELDS * POOL_NS + C_FIELDS * POOL_NC); // [ctx][offset & 15] -> slot
+    unsigned char *freelist = ring + POOL_NC * POOL_RING;
     unsigned char *stagelist = freelist + POOL_NS;
-    unsigned char *ctxfree = stagelist + POOL_NS;
 #define SLF(f, s) Ef[(f) * POOL_NS + (s)]
 #define SLU(f, s) Eu[(f) * POOL_NS + (s)]
-#define CXF(f, c) Cf[(f) * POOL_NC + (c)]
-#define CXU(f, c) Cu[(f) * POOL_NC + (c)]
+#define CXF(f) Cf[(f) * POOL_NC + lane]
+#define CXU(f) Cu[(f) * POOL_NC + lane]
+#define RING(off) ring[lane * POOL_RING + ((off) & (POOL_RING - 1))]
 
     if (!STREAM) {
         for (int i = threadIdx.x; i < qoff; i += POOL_THREADS)
@@ -251,37 +257,29 @@ __global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? 2 : 1)
     }
 #pragma unroll
     for (int k = 0; k < POOL_SPL; ++k)
-        SLU(E_META, lane + 32 * k) = SL_FREE;
-#pragma unroll
-    for (int q = 0; q < POOL_CPL; ++q) {
-        CXU(C_REM, lane + 32 * q) = 0u;
-        CXU(C_J, lane + 32 * q) = 0xffffffffu;
-    }
+        if (lane + 32 * k < POOL_NS)
+            SLU(E_META, lane + 32 * k) = SL_FREE;
+    CXU(C_REM) = 0u;
     __syncthreads();
 
-    const unsigned npix = w.list ? *w.list_count : (unsigned)(a.out_w * a.out_h);
+    const unsigned npix = *w.list_count;
     const unsigned total = npix * (unsigned)w.planes;
     if (a.prog != nullptr && blockIdx.x == 0 && (int)threadIdx.x < a.prog_chunks && a.prog[threadIdx.x] == 0)
         *(volatile unsigned *)&a.prog[2 * a.prog_chunks + threadIdx.x] = 1u; // chunks without hit pixels are final already
-    const bool has_rec = w.rec != nullptr;
-    const bool spec = has_rec && w.spec != 0;
+    const bool spec = w.spec != 0;
     const unsigned nwarps = gridDim.x * WARPS;
     // pixels this warp holds at a time: its share of the list, so that a short list is spread over all warps (the
     // free slots then run the pixels' samples in parallel) and a long one is taken a few pixels at a time
-    int maxctx = (int)min((unsigned long long)POOL_NC,
-                          ((unsigned long long)total + (unsigned long long)nwarps * w.ctx_share_div - 1) /
-                              ((unsigned long long)nwarps * w.ctx_share_div));
-    if (maxctx < 1)
-        maxctx = 1;
-    if (!spec)
-        maxctx = POOL_NC;
+    const int maxctx = (int)max(1ull, min((unsigned long long)POOL_NC,
+                                          ((unsigned long long)total + (unsigned long long)nwarps * w.ctx_share_div - 1) /
+                                              ((unsigned long long)nwarps * w.ctx_share_div)));
     const float fh = (float)(a.H / 2);
     const float wgt = (float)(1.0 / (double)a.spp); // main.c:99
 
     bool exhausted = total == 0;
     unsigned seen = 0; // the list position after this warp's last fetch
-    unsigned long long nrays = 0, nhitpix = 0, iters = 0;
-    unsigned long long st_eval = 0, st_shade_pass = 0, st_shade_lanes = 0, st_sweep_pass = 0, st_sweep_rays = 0;
+    unsigned long long nrays = 0, iters = 0;
+    unsigned st_eval = 0, st_shade_pass = 0, st_shade_lanes = 0, st_sweep_pass = 0, st_sweep_rays = 0;
     unsigned viol = 0;
     uint32_t k0 = 0; // tiles consumed so far (STREAM)
     bool tripped = false;
@@ -297,288 +295,222 @@ __global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? 2 : 1)
         tma_load_1d(stage + qoff, a.sc.geo + (size_t)t * tile * 3, bg, &bars[k & 1]);
     };
 
-    // the pixel's last sample is consumed: write it (vec3ToColor, raytracing.c:11-15)
-    auto finish_pixel = [&](int c) {
-        const int pix = (int)CXU(C_PIX, c), plane = (int)CXU(C_PLANE, c);
-        const f3 acc = mk3(CXF(C_AX, c), CXF(C_AY, c), CXF(C_AZ, c));
-        if (a.accum != nullptr) {
-            float *p = a.accum + ((size_t)plane * a.out_w * a.out_h + pix) * 3;
-            p[0] = acc.x;
-            p[1] = acc.y;
-            p[2] = acc.z;
-        }
-        if (a.rgb != nullptr && a.nsplit == 1) {
-            uint8_t *p = a.rgb + pixel_offset(a, pix);
-            p[0] = (uint8_t)float_to_uint8(acc.x);
-            p[1] = (uint8_t)float_to_uint8(acc.y);
-            p[2] = (uint8_t)float_to_uint8(acc.z);
-            if (a.prog != nullptr) { // the chunk's last finished pixel releases its rows to the copy engine
-                const int ch = (pix / a.out_w) / a.prog_rows, K = a.prog_chunks;
-                __threadfence();
-                if (atomicAdd(&a.prog[K + ch], 1u) + 1u == a.prog[ch]) {
-                    __threadfence_system();
-                    *(volatile unsigned *)&a.prog[2 * K + ch] = 1u;
-                }
-            }
-        }
-    };
-
-    // ---- consume: finished slots in offset order, skipped offsets dropped -----------------------------------
+    // ---- consume: lane c walks its context; finished slots in offset order, skipped offsets dropped --------------
     auto consume = [&]() {
-        while (true) {
-            int act[POOL_SPL]; // 0 nothing, 1 cancel, 2 consume
-            bool any = false;
-#pragma unroll
-            for (int k = 0; k < POOL_SPL; ++k) {
-                const int s = lane + 32 * k;
-                const unsigned m = SLU(E_META, s);
-                act[k] = 0;
-                if ((m & 3u) != SL_FREE) {
-                    const unsigned j = CXU(C_J, (m >> 3) & 255u), off = SLU(E_OFF, s);
-                    if (off < j)
-                        act[k] = 1; // a skipped offset, or the pixel is finished (j = 0xffffffff)
-                    else if ((m & 3u) == SL_DONE && off == j)
-                        act[k] = 2;
-                    any = any || act[k] != 0;
-                }
-            }
-            if (!__any_sync(0xffffffffu, any))
+        unsigned rem = CXU(C_REM);
+        if (rem == 0u)
+            return;
+        unsigned j = CXU(C_J), top = CXU(C_TOP);
+        if (j == top || (SLU(E_META, RING(j)) & 3u) != SL_DONE)
+            return;
+        f3 acc = mk3(CXF(C_AX), CXF(C_AY), CXF(C_AZ));
+        unsigned ts = CXU(C_TSTATE);
+        while (j < top) {
+            const int s = RING(j);
+            const unsigned m = SLU(E_META, s);
+            if ((m & 3u) != SL_DONE)
                 break;
-            __syncwarp();
-#pragma unroll
-            for (int k = 0; k < POOL_SPL; ++k) {
-                const int s = lane + 32 * k;
-                if (act[k] == 2) { // one slot per context at most: offsets of a context are distinct
-                    const unsigned m = SLU(E_META, s);
-                    const int c = (int)((m >> 3) & 255u);
-                    const f3 acc = xadd3(mk3(CXF(C_AX, c), CXF(C_AY, c), CXF(C_AZ, c)), mk3(SLF(E_LX, s), SLF(E_LY, s), SLF(E_LZ, s))); // main.c:99
-                    CXF(C_AX, c) = acc.x;
-                    CXF(C_AY, c) = acc.y;
-                    CXF(C_AZ, c) = acc.z;
-                    nrays += SLU(E_BEST, s); // sweeps of this sample
-                    const unsigned nj = CXU(C_J, c) + (spec ? ((m >> 19) & 255u) : 1u);
-                    if (nj >= CXU(C_TOP, c)) {
-                        CXU(C_TOP, c) = nj;
-                        CXU(C_TSTATE, c) = SLU(E_RNG, s); // the state after this sample = the state at offset nj
-                    }
-                    const unsigned rem = CXU(C_REM, c) - 1u;
-                    CXU(C_REM, c) = rem;
-                    CXU(C_J, c) = nj;
-                    if (rem == 0u) {
-                        finish_pixel(c);
-                        CXU(C_J, c) = 0xffffffffu; // the context's other slots drop out at the next pass
+            acc = xadd3(acc, mk3(SLF(E_LX, s), SLF(E_LY, s), SLF(E_LZ, s))); // main.c:99, in sample order
+            nrays += SLU(E_BEST, s);                                         // sweeps of this sample
+            SLU(E_META, s) = SL_FREE;
+            const unsigned nj = j + (spec ? ((m >> 19) & 255u) : 1u);
+            for (unsigned o = j + 1u; o < nj && o < top; ++o) // offsets this sample skipped
+                SLU(E_META, RING(o)) = SL_FREE;
+            if (nj >= top) {
+                top = nj;
+                ts = SLU(E_RNG, s); // the state after this sample = the state at offset nj
+            }
+            j = nj;
+            if (--rem == 0u)
+                break;
+        }
+        CXF(C_AX) = acc.x;
+        CXF(C_AY) = acc.y;
+        CXF(C_AZ) = acc.z;
+        CXU(C_J) = j;
+        CXU(C_TOP) = top;
+        CXU(C_TSTATE) = ts;
+        CXU(C_REM) = rem;
+        if (rem == 0u) { // the pixel's last sample is consumed: drop what was speculated beyond it, write the pixel
+            for (unsigned o = j; o < top; ++o)
+                SLU(E_META, RING(o)) = SL_FREE;
+            const int pix = (int)CXU(C_PIX), plane = (int)CXU(C_PLANE);
+            if (a.accum != nullptr) {
+                float *p = a.accum + ((size_t)plane * a.out_w * a.out_h + pix) * 3;
+                p[0] = acc.x;
+                p[1] = acc.y;
+                p[2] = acc.z;
+            }
+            if (a.rgb != nullptr && a.nsplit == 1) { // vec3ToColor, raytracing.c:11-15
+                uint8_t *p = a.rgb + pixel_offset(a, pix);
+                p[0] = (uint8_t)float_to_uint8(acc.x);
+                p[1] = (uint8_t)float_to_uint8(acc.y);
+                p[2] = (uint8_t)float_to_uint8(acc.z);
+                if (a.prog != nullptr) { // the chunk's last finished pixel releases its rows to the copy engine
+                    const int ch = (pix / a.out_w) / a.prog_rows, K = a.prog_chunks;
+                    __threadfence();
+                    if (atomicAdd(&a.prog[K + ch], 1u) + 1u == a.prog[ch]) {
+                        __threadfence_system();
+                        *(volatile unsigned *)&a.prog[2 * K + ch] = 1u;
                     }
                 }
-                if (act[k] != 0)
-                    SLU(E_META, s) = SL_FREE;
             }
-            __syncwarp();
         }
     };
 
-    // ---- refill -------------------------------------------------------------------------------------------
+    // ---- refill: new pixels for idle contexts, slots for the offsets the contexts want ---------------------------
     auto refill = [&]() {
-        unsigned fb[POOL_SPL];
         int nfree = 0;
 #pragma unroll
         for (int k = 0; k < POOL_SPL; ++k) {
-            fb[k] = __ballot_sync(0xffffffffu, (SLU(E_META, lane + 32 * k) & 3u) == SL_FREE);
-            if ((fb[k] >> lane) & 1u)
-                freelist[nfree + __popc(fb[k] & lt)] = (unsigned char)(lane + 32 * k);
-            nfree += __popc(fb[k]);
+            const unsigned fb = __ballot_sync(0xffffffffu, lane + 32 * k < POOL_NS && (SLU(E_META, lane + 32 * k) & 3u) == SL_FREE);
+            if ((fb >> lane) & 1u)
+                freelist[nfree + __popc(fb & lt)] = (unsigned char)(lane + 32 * k);
+            nfree += __popc(fb);
         }
-        if (nfree == 0)
-            return;
-        // contexts: live ones, and those with nothing outstanding
-        unsigned lb[POOL_CPL];
-        int nlive = 0, nd1 = 0, nfreectx = 0;
-#pragma unroll
-        for (int q = 0; q < POOL_CPL; ++q) {
-            const int c = lane + 32 * q;
-            const bool live = CXU(C_REM, c) != 0u;
-            lb[q] = __ballot_sync(0xffffffffu, live);
-            nd1 += __popc(__ballot_sync(0xffffffffu, live && CXU(C_TOP, c) == CXU(C_J, c)));
-            if (!live)
-                ctxfree[nfreectx + __popc(~lb[q] & lt)] = (unsigned char)c;
-            nlive += __popc(lb[q]);
-            nfreectx += __popc(~lb[q]);
-        }
-        __syncwarp(); // freelist / ctxfree are read by other lanes below
-        // new pixels from the list
-        int nnew = min(min(nfree - nd1, maxctx - nlive), nfreectx);
-        if (!exhausted && nnew > 0) {
+        unsigned rem = CXU(C_REM);
+        const unsigned idle = __ballot_sync(0xffffffffu, rem == 0u);
+        if (!exhausted && idle != 0u) {
+            const int nlive = 32 - __popc(idle);
             // guided: towards the end of the list the warps take fewer pixels at a time
             const unsigned left = total - min(seen, total);
             const unsigned guide = max(1u, left / (2u * nwarps));
-            nnew = (int)min((unsigned)nnew, guide);
-            unsigned base = 0;
-            if (lane == 0)
-                base = atomicAdd(w.cursor, (unsigned)nnew);
-            base = __shfl_sync(0xffffffffu, base, 0);
-            seen = base + (unsigned)nnew;
-            if (base >= total) {
-                exhausted = true;
-                nnew = 0;
-            } else if (base + (unsigned)nnew > total) {
-                nnew = (int)(total - base);
-            }
-            for (int i = lane; i < nnew; i += 32) {
-                const int c = ctxfree[i];
-                const unsigned t = base + (unsigned)i;
-                const int plane = (int)(t / npix);
-                const unsigned li = t % npix;
-                const int pix = w.list ? w.list[li] : (int)li;
-                const int ci = pix % a.out_w, cj = pix / a.out_w;
-                const int x = a.col_start + ci * a.col_step;
-                const int y = a.row_start + (cj / a.band_h) * a.row_step + (cj % a.band_h);
-                const int g = a.split_first + plane;
-                const float dx = xdiv((float)(x - a.W / 2), fh), dy = xdiv((float)(y - a.H / 2), fh); // main.c:88-94
-                const f3 pdir = xnormalize(xadd3(xadd3(xscale3(a.ex, dx), xscale3(a.ey, dy)), xscale3(a.ez, a.fov)));
-                const int s_begin = (int)((long long)g * a.spp / a.nsplit), s_end = (int)((long long)(g + 1) * a.spp / a.nsplit);
-                const unsigned rem = (unsigned)(s_end - s_begin);
-                CXU(C_PIX, c) = (unsigned)pix;
-                CXU(C_PLANE, c) = (unsigned)plane;
-                CXU(C_REM, c) = rem;
-                CXU(C_TOTAL, c) = rem;
-                CXU(C_J, c) = 0u;
-                CXU(C_TOP, c) = 0u;
-                CXU(C_TSTATE, c) = (uint32_t)(x + y * a.W) + (uint32_t)g * (uint32_t)(a.W * a.H); // main.c:95
-                CXF(C_AX, c) = 0.f;
-                CXF(C_AY, c) = 0.f;
-                CXF(C_AZ, c) = 0.f;
-                CXF(C_DX, c) = pdir.x;
-                CXF(C_DY, c) = pdir.y;
-                CXF(C_DZ, c) = pdir.z;
-                if (has_rec) {
-                    const float2 r = w.rec[li];
-                    CXF(C_BEST0, c) = r.x;
-                    CXU(C_ID0, c) = __float_as_uint(r.y);
-                }
-                if (rem == 0u) { // empty sample range: the partial sum is zero, nothing to trace
-                    if (a.accum != nullptr) {
+            const int nnew = min(max(0, min(__popc(idle), maxctx - nlive)), (int)min(guide, 32u));
+            if (nnew > 0) {
+                unsigned base = 0;
+                if (lane == 0)
+                    base = atomicAdd(w.cursor, (unsigned)nnew);
+                base = __shfl_sync(0xffffffffu, base, 0);
+                seen = base + (unsigned)nnew;
+                if (base >= total)
+                    exhausted = true;
+                const unsigned t = base + (unsigned)__popc(idle & lt);
+                if (rem == 0u && __popc(idle & lt) < nnew && t < total) {
+                    const int plane = (int)(t / npix);
+                    const unsigned li = t % npix;
+                    const int pix = w.list[li];
+                    const float2 hit = w.rec[li];
+                    const int ci = pix % a.out_w, cj = pix / a.out_w;
+                    const int x = a.col_start + ci * a.col_step;
+                    const int y = a.row_start + (cj / a.band_h) * a.row_step + (cj % a.band_h);
+                    const int g = a.split_first + plane;
+                    const float dx = xdiv((float)(x - a.W / 2), fh), dy = xdiv((float)(y - a.H / 2), fh); // main.c:88-94
+                    const f3 pdir = xnormalize(xadd3(xadd3(xscale3(a.ex, dx), xscale3(a.ey, dy)), xscale3(a.ez, a.fov)));
+                    const int s_begin = (int)((long long)g * a.spp / a.nsplit), s_end = (int)((long long)(g + 1) * a.spp / a.nsplit);
+                    rem = (unsigned)(s_end - s_begin);
+                    CXU(C_PIX) = (unsigned)pix;
+                    CXU(C_PLANE) = (unsigned)plane;
+                    CXU(C_REM) = rem;
+                    CXU(C_TOTAL) = rem;
+                    CXU(C_J) = 0u;
+                    CXU(C_TOP) = 0u;
+                    CXU(C_TSTATE) = (uint32_t)(x + y * a.W) + (uint32_t)g * (uint32_t)(a.W * a.H); // main.c:95
+                    CXF(C_AX) = 0.f;
+                    CXF(C_AY) = 0.f;
+                    CXF(C_AZ) = 0.f;
+                    CXF(C_DX) = pdir.x;
+                    CXF(C_DY) = pdir.y;
+                    CXF(C_DZ) = pdir.z;
+                    CXF(C_BEST0) = hit.x;
+                    CXU(C_ID0) = __float_as_uint(hit.y);
+                    if (rem == 0u && a.accum != nullptr) { // empty sample range: the partial sum is zero, nothing to trace
                         float *p = a.accum + ((size_t)plane * a.out_w * a.out_h + pix) * 3;
                         p[0] = p[1] = p[2] = 0.f;
                     }
-                    CXU(C_J, c) = 0xffffffffu;
                 }
             }
-            __syncwarp();
         }
-        // grants: one slot for every live context with nothing outstanding, then speculative children
-        int g1[POOL_CPL], g2[POOL_CPL], want2[POOL_CPL];
-        int n1 = 0, nwant2 = 0, mine1 = 0;
-#pragma unroll
-        for (int q = 0; q < POOL_CPL; ++q) {
-            const int c = lane + 32 * q;
-            const unsigned rem = CXU(C_REM, c), j = CXU(C_J, c), top = CXU(C_TOP, c);
-            const bool live = rem != 0u;
-            g1[q] = (live && top == j) ? 1 : 0;
-            want2[q] = 0;
-            if (spec && live) {
+        if (nfree == 0)
+            return;
+        // demand of this lane's context: one slot when nothing is outstanding (the reference's serial stream), and
+        // speculative children at the next unassigned offsets as far as they can still be needed
+        unsigned j = 0, top = 0;
+        int first = 0, extra = 0;
+        if (rem != 0u) {
+            j = CXU(C_J);
+            top = CXU(C_TOP);
+            first = top == j ? 1 : 0;
+            if (spec) {
                 // offsets below j + rem can still be needed; a pixel that keeps skipping (closed scenes) runs serially
-                const unsigned consumed = CXU(C_TOTAL, c) - rem, skipped = j - consumed;
+                const unsigned consumed = CXU(C_TOTAL) - rem, skipped = j - consumed;
                 if (skipped * 2u <= consumed + 4u)
-                    want2[q] = max(0, (int)(j + rem - top) - g1[q]);
+                    extra = max(0, min((int)(j + rem - top), POOL_RING - (int)(top - j)) - first);
             }
-            n1 += __popc(__ballot_sync(0xffffffffu, g1[q] != 0));
-            nwant2 += __popc(__ballot_sync(0xffffffffu, want2[q] > 0));
-            mine1 += g1[q];
         }
-        const int left = nfree - n1;
-        const int quota = (left > 0 && nwant2 > 0) ? (left + nwant2 - 1) / nwant2 : 0;
-        int mine2 = 0;
-#pragma unroll
-        for (int q = 0; q < POOL_CPL; ++q) {
-            g2[q] = min(want2[q], quota);
-            mine2 += g2[q];
-        }
-        // positions in the free list: class 1 first, then class 2, each in (lane, q) order
-        int p1 = mine1, p2 = mine2;
+        const unsigned fm = __ballot_sync(0xffffffffu, first != 0);
+        const int n1 = __popc(fm);
+        const int nwant = __popc(__ballot_sync(0xffffffffu, extra > 0));
+        const int left2 = nfree - n1;
+        extra = (left2 > 0 && nwant > 0) ? min(extra, (left2 + nwant - 1) / nwant) : 0;
+        int p2 = extra; // inclusive scan of the extras
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            const int v1 = __shfl_up_sync(0xffffffffu, p1, o), v2 = __shfl_up_sync(0xffffffffu, p2, o);
-            if (lane >= o) {
-                p1 += v1;
-                p2 += v2;
-            }
+            const int v = __shfl_up_sync(0xffffffffu, p2, o);
+            if (lane >= o)
+                p2 += v;
         }
-        const int tot2 = __shfl_sync(0xffffffffu, p2, 31);
-        p1 -= mine1;              // exclusive
-        p2 = n1 + (p2 - mine2);   // exclusive, behind class 1
-        const int nassigned = min(nfree, n1 + tot2);
-#pragma unroll
-        for (int q = 0; q < POOL_CPL; ++q) {
-            const int c = lane + 32 * q;
-            const int ga = (g1[q] && p1 < nfree) ? 1 : 0;
-            const int gb = max(0, min(g2[q], nfree - p2));
-            if (ga + gb > 0) {
-                unsigned top = CXU(C_TOP, c), ts = CXU(C_TSTATE, c);
-                for (int i = 0; i < ga + gb; ++i) {
-                    const int s = freelist[i < ga ? p1 : p2 + (i - ga)];
-                    SLU(E_OFF, s) = top;
-                    SLU(E_RNG, s) = ts;
-                    SLU(E_META, s) = 0x80000000u | ((unsigned)c << 3); // to be initialised below
-                    top += 1u;
-                    if (spec)
-                        ts = ts * LCG7_M + LCG7_C; // the state 7 draws later = the next offset's
-                }
-                CXU(C_TOP, c) = top;
-                CXU(C_TSTATE, c) = ts;
+        p2 = n1 + p2 - extra; // this lane's first extra position in the free list, behind the firsts
+        const int p1 = __popc(fm & lt);
+        const int ga = (first && p1 < nfree) ? 1 : 0;
+        const int gb = max(0, min(extra, nfree - p2));
+        __syncwarp(); // the free list is complete
+        if (ga + gb > 0) {
+            unsigned ts = CXU(C_TSTATE);
+            const f3 pd = mk3(CXF(C_DX), CXF(C_DY), CXF(C_DZ));
+            const float best0 = CXF(C_BEST0);
+            const unsigned id0 = CXU(C_ID0);
+            for (int i = 0; i < ga + gb; ++i) {
+                const int s = freelist[i < ga ? p1 : p2 + (i - ga)];
+                SLF(E_PX, s) = a.origin.x;
+                SLF(E_PY, s) = a.origin.y;
+                SLF(E_PZ, s) = a.origin.z;
+                SLF(E_DX, s) = pd.x;
+                SLF(E_DY, s) = pd.y;
+                SLF(E_DZ, s) = pd.z;
+                SLF(E_TX, s) = 1.f;
+                SLF(E_TY, s) = 1.f;
+                SLF(E_TZ, s) = 1.f;
+                SLF(E_LX, s) = 0.f;
+                SLF(E_LY, s) = 0.f;
+                SLF(E_LZ, s) = 0.f;
+                SLU(E_RNG, s) = ts;
+                SLF(E_BEST, s) = best0; // the primary hit is known (the primary kernel sweeps that ray every sample)
+                SLU(E_ID, s) = id0;
+                SLU(E_META, s) = meta_make(SL_SHADE, 0u, 0u);
+                RING(top) = (unsigned char)s;
+                top += 1u;
+                if (spec)
+                    ts = ts * LCG7_M + LCG7_C; // the state 7 draws later = the next offset's
             }
-            p1 += g1[q];
-            p2 += g2[q];
+            CXU(C_TOP) = top;
+            CXU(C_TSTATE) = ts;
+            st_eval += (unsigned)(ga + gb);
         }
-        __syncwarp();
-        // initialise the assigned slots, one per lane at a time
-        for (int i = lane; i < nassigned; i += 32) {
-            const int s = freelist[i];
-            const unsigned m = SLU(E_META, s);
-            if (!(m & 0x80000000u))
-                continue; // (a class-1 position that was not granted: cannot happen, n1 <= nfree is not guaranteed)
-            const int c = (int)((m >> 3) & 255u);
-            SLF(E_PX, s) = a.origin.x;
-            SLF(E_PY, s) = a.origin.y;
-            SLF(E_PZ, s) = a.origin.z;
-            SLF(E_DX, s) = CXF(C_DX, c);
-            SLF(E_DY, s) = CXF(C_DY, c);
-            SLF(E_DZ, s) = CXF(C_DZ, c);
-            SLF(E_TX, s) = 1.f;
-            SLF(E_TY, s) = 1.f;
-            SLF(E_TZ, s) = 1.f;
-            SLF(E_LX, s) = 0.f;
-            SLF(E_LY, s) = 0.f;
-            SLF(E_LZ, s) = 0.f;
-            if (has_rec) { // the primary hit is known (the primary kernel sweeps that ray every sample)
-                SLF(E_BEST, s) = CXF(C_BEST0, c);
-                SLU(E_ID, s) = CXU(C_ID0, c);
-                SLU(E_META, s) = meta_make(SL_SHADE, (unsigned)c, 0u, 0u);
-            } else {
-                const bool first = w.write_ids && SLU(E_OFF, s) == 0u && CXU(C_PLANE, c) == 0u;
-                SLU(E_META, s) = meta_make(SL_SWEEP, (unsigned)c, 0u, 0u, first ? SL_FIRST : 0u);
-            }
-            st_eval++;
-        }
-        __syncwarp();
     };
 
-    // ---- shade: calcColor's loop body for up to 32 slots whose ray hit ------------------------------------
+    // ---- shade: calcColor's loop body for up to 64 slots whose ray hit, two per lane one after the other ------------
     auto shade_stage = [&](const unsigned (&sb)[POOL_SPL]) {
         int n = 0;
 #pragma unroll
         for (int k = 0; k < POOL_SPL; ++k) {
             if ((sb[k] >> lane) & 1u) {
                 const int pos = n + __popc(sb[k] & lt);
-                if (pos < 32)
+                if (pos < 64)
                     stagelist[pos] = (unsigned char)(lane + 32 * k);
             }
             n += __popc(sb[k]);
         }
-        n = min(n, 32);
+        n = n >= 64 ? 64 : min(n, 32); // full passes only
         __syncwarp();
-        st_shade_pass++;
-        st_shade_lanes += lane < n;
-        if (lane < n) {
-            const int s = stagelist[lane];
+#pragma unroll 1
+        for (int r = 0; r < 2; ++r) {
+            if (32 * r >= n)
+                break;
+            st_shade_pass++;
+            st_shade_lanes += lane + 32 * r < n;
+            if (lane + 32 * r >= n)
+                continue;
+            const int s = stagelist[lane + 32 * r];
             const unsigned m = SLU(E_META, s);
             Lane L;
             L.pos = mk3(SLF(E_PX, s), SLF(E_PY, s), SLF(E_PZ, s));
@@ -591,12 +523,8 @@ __global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? 2 : 1)
             const bool done = shade_hit(L, a, SLF(E_BEST, s), (int)SLU(E_ID, s));
             SLU(E_RNG, s) = L.rng;
             if (done) { // Russian roulette or the bounce limit: the sample's light, scaled as main.c:99 does
-                const f3 c = xscale3(L.light, wgt);
-                SLF(E_LX, s) = c.x;
-                SLF(E_LY, s) = c.y;
-                SLF(E_LZ, s) = c.z;
-                SLU(E_BEST, s) = hits - (has_rec ? 1u : 0u); // sweeps of this sample by this kernel
-                SLU(E_META, s) = meta_make(SL_DONE, (m >> 3) & 255u, 0u, hits);
+                L.light = xscale3(L.light, wgt);
+                SLU(E_BEST, s) = hits - 1u; // sweeps of this sample by this kernel
             } else {
                 SLF(E_PX, s) = L.pos.x;
                 SLF(E_PY, s) = L.pos.y;
@@ -607,37 +535,35 @@ __global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? 2 : 1)
                 SLF(E_TX, s) = L.tint.x;
                 SLF(E_TY, s) = L.tint.y;
                 SLF(E_TZ, s) = L.tint.z;
-                SLF(E_LX, s) = L.light.x;
-                SLF(E_LY, s) = L.light.y;
-                SLF(E_LZ, s) = L.light.z;
-                SLU(E_META, s) = meta_make(SL_SWEEP, (m >> 3) & 255u, (unsigned)L.bounce, hits);
             }
+            SLF(E_LX, s) = L.light.x;
+            SLF(E_LY, s) = L.light.y;
+            SLF(E_LZ, s) = L.light.z;
+            SLU(E_META, s) = meta_make(done ? SL_DONE : SL_SWEEP, (unsigned)L.bounce, hits);
         }
-        __syncwarp();
     };
 
-    // ---- sweep: closest hit of up to 64 rays, NR per lane; misses take the sky at once -------------------------
-    auto sweep_stage = [&](const unsigned (&wb)[POOL_SPL], auto nr_tag) {
-        constexpr int NR = decltype(nr_tag)::value;
+    // ---- sweep: closest hit of up to 64 rays, two per lane; misses take the sky at once -------------------------
+    auto sweep_stage = [&](const unsigned (&wb)[POOL_SPL]) {
         int n = 0;
 #pragma unroll
         for (int k = 0; k < POOL_SPL; ++k) {
             if ((wb[k] >> lane) & 1u) {
                 const int pos = n + __popc(wb[k] & lt);
-                if (pos < 32 * NR)
+                if (pos < 64)
                     stagelist[pos] = (unsigned char)(lane + 32 * k);
             }
             n += __popc(wb[k]);
         }
-        n = min(n, 32 * NR);
+        n = min(n, 64);
         __syncwarp();
-        int s_[NR];
-        bool act[NR];
-        f3 o[NR], d[NR];
-        float best[NR];
-        int bestId[NR];
+        int s_[2];
+        bool act[2];
+        f3 o[2], d[2];
+        float best[2];
+        int bestId[2];
 #pragma unroll
-        for (int r = 0; r < NR; ++r) {
+        for (int r = 0; r < 2; ++r) {
             act[r] = lane + 32 * r < n;
             s_[r] = act[r] ? (int)stagelist[lane + 32 * r] : 0;
             o[r] = mk3(SLF(E_PX, s_[r]), SLF(E_PY, s_[r]), SLF(E_PZ, s_[r]));
@@ -649,11 +575,9 @@ __global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? 2 : 1)
                     sphere_test_exact(o[r], d[r], __ldg(&a.sc.s0[k]), k, best[r], bestId[r]);
         }
         st_sweep_pass++;
-#pragma unroll
-        for (int r = 0; r < NR; ++r)
-            st_sweep_rays += act[r];
+        st_sweep_rays += (unsigned)act[0] + (unsigned)act[1];
         if (!STREAM) {
-            sweep_multi<MODE, NR, NR == 2 ? 4 : 8>(sGeo, sGeo + qoff, w.obound, ntris, 0, act, o, d, best, bestId, viol);
+            sweep_two<MODE>(sGeo, sGeo + qoff, w.obound, ntris, 0, act, o, d, best, bestId, viol);
         } else {
             if (threadIdx.x == 0) {
                 issue(k0, 0);
@@ -665,8 +589,7 @@ __global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? 2 : 1)
                 mbar_wait(&bars[k & 1], (k >> 1) & 1u);
                 const float4 *stage = sGeo + (size_t)(k & 1) * STAGE_F4;
                 if (n > 0)
-                    sweep_multi<MODE, NR, 4>(stage, stage + qoff, w.obound, min(tile, ntris - t * tile), t * tile, act, o, d,
-                                             best, bestId, viol);
+                    sweep_two<MODE>(stage, stage + qoff, w.obound, min(tile, ntris - t * tile), t * tile, act, o, d, best, bestId, viol);
                 __syncthreads(); // every warp is done with this stage
                 if (threadIdx.x == 0 && t + 2 < ntiles)
                     issue(k + 2, t + 2);
@@ -676,25 +599,18 @@ __global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? 2 : 1)
         // results go to the slots first, so that the (divergent, FP64) epilogue below is one copy of the code looping
         // over the lane's rays without indexing registers dynamically
 #pragma unroll
-        for (int r = 0; r < NR; ++r)
+        for (int r = 0; r < 2; ++r)
             if (act[r]) {
                 SLF(E_BEST, s_[r]) = best[r];
                 SLU(E_ID, s_[r]) = (unsigned)bestId[r];
             }
 #pragma unroll 1
-        for (int r = 0; r < NR; ++r) {
+        for (int r = 0; r < 2; ++r) {
             if (lane + 32 * r >= n)
                 continue;
             const int s = (int)stagelist[lane + 32 * r];
             const unsigned m = SLU(E_META, s);
-            const int c = (int)((m >> 3) & 255u);
-            const int id = (int)SLU(E_ID, s);
-            if (m & SL_FIRST) { // this kernel owns the id map: the pixel's first primary sweep
-                if (a.ids != nullptr)
-                    a.ids[CXU(C_PIX, c)] = id;
-                nhitpix += id != -1;
-            }
-            if (id == -1) { // miss: sky, the path ends (raytracing.c:289-293)
+            if ((int)SLU(E_ID, s) == -1) { // miss: sky, the path ends (raytracing.c:289-293)
                 Lane L;
                 L.dir = mk3(SLF(E_DX, s), SLF(E_DY, s), SLF(E_DZ, s));
                 L.tint = mk3(SLF(E_TX, s), SLF(E_TY, s), SLF(E_TZ, s));
@@ -704,41 +620,40 @@ __global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? 2 : 1)
                 SLF(E_LX, s) = cc.x;
                 SLF(E_LY, s) = cc.y;
                 SLF(E_LZ, s) = cc.z;
-                const unsigned hits = (m >> 19) & 255u;
-                SLU(E_BEST, s) = hits + (has_rec ? 0u : 1u); // sweeps of this sample by this kernel
-                SLU(E_META, s) = meta_make(SL_DONE, (unsigned)c, 0u, hits);
+                SLU(E_BEST, s) = (m >> 19) & 255u; // sweeps of this sample by this kernel
+                SLU(E_META, s) = (m & ~3u) | SL_DONE;
             } else {
-                SLU(E_META, s) = (m & ~(3u | SL_FIRST)) | SL_SHADE;
+                SLU(E_META, s) = (m & ~3u) | SL_SHADE;
             }
         }
-        __syncwarp();
     };
 
     // ---- the scheduler ------------------------------------------------------------------------------------
     while (true) {
         bool sweep_due = false;
         unsigned sb[POOL_SPL], wb[POOL_SPL];
-        int nsweep = 0;
         while (true) {
             if (++iters > w.watchdog) {
                 tripped = true;
                 break;
             }
+            __syncwarp();
             consume();
+            __syncwarp();
             refill();
-            int nshade = 0;
-            nsweep = 0;
+            __syncwarp();
+            int nshade = 0, nsweep = 0;
 #pragma unroll
             for (int k = 0; k < POOL_SPL; ++k) {
-                const unsigned st = SLU(E_META, lane + 32 * k) & 3u;
+                const unsigned st = lane + 32 * k < POOL_NS ? SLU(E_META, lane + 32 * k) & 3u : (unsigned)SL_FREE;
                 sb[k] = __ballot_sync(0xffffffffu, st == SL_SHADE);
                 wb[k] = __ballot_sync(0xffffffffu, st == SL_SWEEP);
                 nshade += __popc(sb[k]);
                 nsweep += __popc(wb[k]);
             }
             // the pass that fills its lanes better; a streamed sweep costs a pass over the whole scene: fill it
-            const int esw = STREAM ? (nsweep >= 64 || nshade == 0 ? 64 : 0) : min(64, nsweep > 32 ? nsweep : 2 * nsweep);
-            const int esh = 2 * min(nshade, 32);
+            const int esw = STREAM ? (nsweep >= 64 || nshade == 0 ? 64 : 0) : min(64, nsweep);
+            const int esh = 2 * min(nshade, 32); // (a shade pass takes 64 slots when there are 64, else up to 32)
             if (nsweep > 0 && esw >= esh) {
                 sweep_due = true;
                 break;
@@ -748,11 +663,7 @@ __global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? 2 : 1)
                 continue;
             }
             // nothing to run: finished when the list is exhausted and no pixel is live (else refill has work to hand out)
-            bool live = false;
-#pragma unroll
-            for (int q = 0; q < POOL_CPL; ++q)
-                live = live || CXU(C_REM, lane + 32 * q) != 0u;
-            if (exhausted && !__any_sync(0xffffffffu, live))
+            if (exhausted && !__any_sync(0xffffffffu, CXU(C_REM) != 0u))
                 break;
         }
         if (STREAM) {
@@ -763,18 +674,15 @@ __global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? 2 : 1)
         } else if (!sweep_due) {
             break;
         }
-        if (STREAM || nsweep > 32)
-            sweep_stage(wb, std::integral_constant<int, 2>());
-        else
-            sweep_stage(wb, std::integral_constant<int, 1>());
+        sweep_stage(wb);
     }
     if (tripped && lane == 0)
         atomicExch(w.error, 1u);
 
     if (a.stats != nullptr) {
-        unsigned long long v[8] = {nrays, nhitpix, st_eval, st_shade_pass, st_shade_lanes, st_sweep_pass, st_sweep_rays, iters};
+        unsigned long long v[7] = {nrays, st_eval, st_shade_pass, st_shade_lanes, st_sweep_pass, st_sweep_rays, iters};
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
+        for (int i = 0; i < 7; ++i)
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1)
                 v[i] += __shfl_xor_sync(0xffffffffu, v[i], o);
@@ -789,21 +697,20 @@ __global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? 2 : 1)
                 atomicAdd(&a.stats[ST_SPH_PAIRS], v[0] * (unsigned long long)nsph);
                 atomicAdd(&a.stats[ST_SLOW_PAIRS], v[0] * (unsigned long long)ntris);
             }
-            if (w.write_ids && a.ids != nullptr && v[1])
-                atomicAdd(&a.stats[ST_HIT_PIXELS], v[1]);
             // scheduler counters (per-lane values were summed over the warp: passes and iterations count 32 per warp)
-            atomicAdd(&a.stats[ST_POOL_EVAL], v[2]);
-            atomicAdd(&a.stats[ST_POOL_SHADE_PASSES], v[3] / 32);
-            atomicAdd(&a.stats[ST_POOL_SHADE_LANES], v[4]);
-            atomicAdd(&a.stats[ST_POOL_SWEEP_PASSES], v[5] / 32);
-            atomicAdd(&a.stats[ST_POOL_SWEEP_RAYS], v[6]);
-            atomicAdd(&a.stats[ST_POOL_ITERS], v[7] / 32);
+            atomicAdd(&a.stats[ST_POOL_EVAL], v[1]);
+            atomicAdd(&a.stats[ST_POOL_SHADE_PASSES], v[2] / 32);
+            atomicAdd(&a.stats[ST_POOL_SHADE_LANES], v[3]);
+            atomicAdd(&a.stats[ST_POOL_SWEEP_PASSES], v[4] / 32);
+            atomicAdd(&a.stats[ST_POOL_SWEEP_RAYS], v[5]);
+            atomicAdd(&a.stats[ST_POOL_ITERS], v[6] / 32);
         }
     }
 #undef SLF
 #undef SLU
 #undef CXF
 #undef CXU
+#undef RING
 }
 
 } // namespace rtc
