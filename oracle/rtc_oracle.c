@@ -12,7 +12,7 @@
  *
  * PARITY PINNING: the reference ships no tests or golden vectors for this
  * path.  This restatement is pinned instead against the
- * reference itself: tests/test_oracle_vs_reference.py compares it bit-for-bit
+ * reference itself: tests/test_oracle_golden.py compares it bit-for-bit
  * with oracle/_ref (the reference's own functions, compiled from
  * /root/reference) and tests/golden/ holds the vectors generated that way by
  * tests/golden/make_golden.py.
