@@ -99,7 +99,9 @@ typedef struct RenderParams {
     int32_t nsplit;          /* <= 1: the reference's one RNG stream per pixel.
                                 G > 1: G sub-streams per pixel, sub-stream g seeded
                                 x + y*W + g*W*H renders samples [g*spp/G,(g+1)*spp/G),
-                                partial sums added in g order.          */
+                                partial sums added in g order: this
+                                library's own definition, NOT the reference's image.
+                                RTC_SPLIT_SAMPLES needs it set (a multiple of ngpus). */
     int32_t *out_primary_id; /* optional, width*height: -1 miss, -2-k sphere k, else triangle index */
     RenderStats *stats;      /* optional */
     uint32_t flags;
@@ -124,6 +126,10 @@ void rtc_normalize(const float in[3], float out[3]);
 /* Host code: the synthetic random-triangle scene of BASELINE.json's config 5 (splitmix64, definition in
  * rtc_api.cu / DESIGN.md; the reference has no generator).  The config uses seed 0xB200, ntris 1048576. */
 void rtc_synth_scene(uint64_t seed, int32_t ntris, Triangle *out);
+
+/* Host code: FNV-1a-64 of a byte buffer (offset 1469598103934665603, prime 1099511628211) -- the image hash of the
+ * known-answer vectors (tests/golden/kat.json), so that callers can check a frame without other tooling. */
+uint64_t rtc_fnv1a64(const void *data, size_t nbytes);
 
 /* number of CUDA devices visible (0 if none / no driver) */
 int rtc_device_count(void);
@@ -172,6 +178,11 @@ typedef struct RtcDeviceJob {
     RtcSubset subset;
     int32_t out_w, out_h;  /* compact output size, see rtc_subset_size()              */
     uint32_t flags;
+    int32_t rgb_full;      /* 1: d_rgb is the FULL width x height image (possibly another device's memory, see
+                              rtc_ipc_open): every pixel is stored at its final row and column instead of its
+                              compact position, so the ranks of a tile split assemble the frame by writing it --
+                              no gather, no un-interleave (the reference's row threads fill `Color image[]` the
+                              same way, main.c:84,100)                                 */
 } RtcDeviceJob;
 
 /* compact size of a subset of a width x height image */
@@ -210,8 +221,21 @@ int rtc_quantize_device(int device, const float *d_accum, uint8_t *d_rgb, size_t
  * (bounce rays, shading).  Waits for that render to finish. */
 int rtc_scene_kernel_times(const RtcScene *scene, float *primary_ms, float *paths_ms);
 
-/* number of kernels rtc_render_device launches for this job (for launch accounting) */
+/* number of kernels rtc_render_device launches for this job in the default mode (an estimate by formula; the count
+ * of launches that actually happened is rtc_launches_total) */
 int rtc_render_launch_count(const RtcScene *scene, const RtcDeviceJob *job, int want_ids);
+/* kernels this library has launched since it was loaded (every launch site counts): difference two readings */
+uint64_t rtc_launches_total(void);
+
+/* A device buffer of ANOTHER process as a pointer of this one (CUDA IPC over NVLink / PCIe peer access): the owner
+ * exports a 64-byte handle, peers open it and pass the pointer as d_rgb with RtcDeviceJob.rgb_full = 1.  With one
+ * process per GPU this is how the ranks of a tile split write their pixels straight into the destination frame. */
+#define RTC_IPC_HANDLE_BYTES 64
+int rtc_ipc_export(int device, const void *d_ptr, unsigned char handle[RTC_IPC_HANDLE_BYTES]);
+int rtc_ipc_open(int device, const unsigned char handle[RTC_IPC_HANDLE_BYTES], void **d_ptr);
+int rtc_ipc_close(int device, void *d_ptr);
+/* the same inside one process: let `device` access `peer`'s memory (idempotent) */
+int rtc_enable_peer(int device, int peer);
 
 /* parts [nparts][part_elems] -> image rows: part g holds the band_h-row bands g, g+nparts, ... of an image
  * with `height` rows of `row_elems` elements (elem_size 1 or 4 bytes).  The un-interleave step after an

@@ -78,7 +78,7 @@ class RtcDeviceJob(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("spp", C.c_int32), ("maxBounce", C.c_int32),
                 ("trianglesOnly", C.c_int32), ("nsplit", C.c_int32), ("split_first", C.c_int32),
                 ("split_count", C.c_int32), ("subset", RtcSubset), ("out_w", C.c_int32), ("out_h", C.c_int32),
-                ("flags", C.c_uint32)]
+                ("flags", C.c_uint32), ("rgb_full", C.c_int32)]
 
 
 class RtcError(RuntimeError):
@@ -94,7 +94,8 @@ EXPORTS = ["render_cuda", "render_cuda_shutdown", "rtc_camera_look_at", "rtc_nor
            "rtc_last_error", "rtc_version", "rtc_scene_create", "rtc_scene_destroy", "rtc_subset_size",
            "rtc_render_device", "rtc_sum_quantize_device", "rtc_quantize_device", "rtc_render_launch_count",
            "rtc_uninterleave_device", "rtc_download_bands", "rtc_fp32_peak_probe", "rtc_scene_update", "rtc_scene_kernel_times", "rtc_synth_scene",
-           "rtc_probe_random_direction", "rtc_probe_environment_light"]
+           "rtc_probe_random_direction", "rtc_probe_environment_light", "rtc_launches_total", "rtc_ipc_export",
+           "rtc_ipc_open", "rtc_ipc_close", "rtc_enable_peer", "rtc_fnv1a64"]
 
 
 def load_library() -> C.CDLL:
@@ -159,6 +160,17 @@ def load_library() -> C.CDLL:
     lib.rtc_probe_random_direction.restype = C.c_int
     lib.rtc_probe_environment_light.argtypes = [C.c_int, P(Scene), C.c_void_p, C.c_int32, C.c_void_p]
     lib.rtc_probe_environment_light.restype = C.c_int
+    lib.rtc_launches_total.restype = C.c_uint64
+    lib.rtc_ipc_export.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
+    lib.rtc_ipc_export.restype = C.c_int
+    lib.rtc_ipc_open.argtypes = [C.c_int, C.c_void_p, P(C.c_void_p)]
+    lib.rtc_ipc_open.restype = C.c_int
+    lib.rtc_ipc_close.argtypes = [C.c_int, C.c_void_p]
+    lib.rtc_ipc_close.restype = C.c_int
+    lib.rtc_enable_peer.argtypes = [C.c_int, C.c_int]
+    lib.rtc_enable_peer.restype = C.c_int
+    lib.rtc_fnv1a64.argtypes = [C.c_void_p, C.c_size_t]
+    lib.rtc_fnv1a64.restype = C.c_uint64
     _lib = lib
     return lib
 
@@ -254,6 +266,7 @@ class DeviceJob:
     split_count: int = 0
     subset: tuple = (0, 1, 0, 1, 1)  # row_start, row_step, col_start, col_step, band_h
     flags: int = 0
+    rgb_full: int = 0  # 1: d_rgb is the full image; pixels go to their final row and column
     out_w: int = field(default=0, init=False)
     out_h: int = field(default=0, init=False)
 
@@ -266,6 +279,7 @@ class DeviceJob:
         j.out_w, j.out_h = subset_size(self.width, self.height, j.subset)
         self.out_w, self.out_h = j.out_w, j.out_h
         j.flags = self.flags
+        j.rgb_full = self.rgb_full
         return j
 
     @property
@@ -340,6 +354,41 @@ def download_bands(device: int, d_part: int, h_img: int, row_bytes: int, height:
     """This part's rows of a band split straight into a host image (asynchronous on `stream`)."""
     _check(load_library().rtc_download_bands(device, d_part, h_img, row_bytes, height, nparts, band_h, part,
                                              stream or None))
+
+
+def fnv1a64(a: np.ndarray) -> str:
+    """FNV-1a-64 of an array's bytes, as 16 hex digits (the image hash of tests/golden/kat.json)."""
+    a = np.ascontiguousarray(a)
+    return f"{load_library().rtc_fnv1a64(a.ctypes.data, a.nbytes):016x}"
+
+
+def launches_total() -> int:
+    """Kernels the library has launched since it was loaded (difference two readings)."""
+    return int(load_library().rtc_launches_total())
+
+
+def ipc_export(device: int, d_ptr: int) -> bytes:
+    """64-byte CUDA IPC handle of a device buffer of this process."""
+    h = (C.c_ubyte * 64)()
+    _check(load_library().rtc_ipc_export(device, d_ptr, h))
+    return bytes(h)
+
+
+def ipc_open(device: int, handle: bytes) -> int:
+    """Another process's buffer as a device pointer of this one."""
+    h = (C.c_ubyte * 64).from_buffer_copy(handle)
+    p = C.c_void_p()
+    _check(load_library().rtc_ipc_open(device, h, C.byref(p)))
+    return int(p.value)
+
+
+def ipc_close(device: int, d_ptr: int) -> None:
+    _check(load_library().rtc_ipc_close(device, d_ptr))
+
+
+def enable_peer(device: int, peer: int) -> None:
+    """Let `device` read and write `peer`'s memory (one process driving several GPUs)."""
+    _check(load_library().rtc_enable_peer(device, peer))
 
 
 def synth_scene(ntris: int, seed: int = 0xB200) -> np.ndarray:

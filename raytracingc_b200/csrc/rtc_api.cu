@@ -8,6 +8,10 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <atomic>
+#include <condition_variable>
+#include <functional>
+#include <thread>
 #include <map>
 #include <mutex>
 #include <tuple>
@@ -32,6 +36,10 @@ static_assert(sizeof(Camera) == 52, "Camera is origin, ex, ey, ez, fov");
 namespace {
 
 thread_local char g_err[512] = "";
+
+// kernels launched by this library since it was loaded (every <<< >>> below is followed by count_launch())
+std::atomic<unsigned long long> g_launches{0};
+inline void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 int fail(int code, const char *fmt, ...)
 {
@@ -127,6 +135,15 @@ int rtc_device_count(void)
 }
 
 void rtc_normalize(const float in[3], float out[3]) { host_normalize(in, out); }
+
+uint64_t rtc_fnv1a64(const void *data, size_t nbytes)
+{
+    const unsigned char *p = static_cast<const unsigned char *>(data);
+    uint64_t h = 1469598103934665603ull;
+    for (size_t i = 0; i < nbytes; ++i)
+        h = (h ^ p[i]) * 1099511628211ull;
+    return h;
+}
 
 // reference main.c:252-255
 void rtc_camera_look_at(const float origin[3], const float lookingAt[3], float fov, Camera *out)
@@ -313,11 +330,13 @@ static int scene_upload(RtcScene *sc, const Triangle *tris, int ntris, const Sph
     if (nsph > 0) {
         CU(cudaMemcpyAsync(raw_s, spheres, sizeof(Sphere) * (size_t)nsph, cudaMemcpyHostToDevice, st));
         rtc::flatten_spheres_kernel<<<(nsph + 127) / 128, 128, 0, st>>>(raw_s, nsph, sc->s0, sc->s1, sc->s2);
+        count_launch();
         CU(cudaGetLastError());
     }
     if (ntris > 0) {
         CU(cudaMemcpyAsync(raw_t, tris, sizeof(Triangle) * (size_t)ntris, cudaMemcpyHostToDevice, st));
         rtc::flatten_kernel<<<(ntris + 127) / 128, 128, 0, st>>>(raw_t, ntris, sc->geo, sc->m0, sc->m1);
+        count_launch();
         CU(cudaGetLastError());
     }
     return RTC_OK;
@@ -371,6 +390,24 @@ int check_job(const RtcScene *sc, const Scene *sky, const Camera *cam, const Rtc
         return fail(RTC_ERR_ARG, "render: height must be >= 2 (the reference divides by height/2, main.c:88)");
     if (job->out_w < 0 || job->out_h < 0)
         return fail(RTC_ERR_ARG, "render: negative output size");
+    if (job->subset.row_start < 0 || job->subset.col_start < 0)
+        return fail(RTC_ERR_ARG, "render: negative subset origin");
+    {
+        // the compact size must be the subset's: a larger out_h would write outside the caller's buffers
+        int32_t w = 0, h = 0;
+        rtc_subset_size(job->width, job->height, &job->subset, &w, &h);
+        if (w != job->out_w || h != job->out_h)
+            return fail(RTC_ERR_ARG, "render: out_w x out_h = %d x %d but the subset has %d x %d pixels (rtc_subset_size)",
+                        job->out_w, job->out_h, w, h);
+    }
+    {
+        const long long G = job->nsplit > 1 ? job->nsplit : 1;
+        const long long planes = job->split_count > 0 ? job->split_count : G - job->split_first;
+        if (planes > 65535)
+            return fail(RTC_ERR_ARG, "render: at most 65535 sub-streams per call (got %lld)", planes);
+        if ((long long)job->out_w * job->out_h * (planes > 0 ? planes : 1) >= (1ll << 31))
+            return fail(RTC_ERR_ARG, "render: out_w * out_h * sub-streams must stay below 2^31 (32-bit task counters)");
+    }
     return RTC_OK;
 }
 
@@ -415,6 +452,7 @@ rtc::RenderArgs make_args(const RtcScene *sc, const Scene *sky, const Camera *ca
     a.band_h = job->subset.band_h > 0 ? job->subset.band_h : 1;
     a.out_w = job->out_w;
     a.out_h = job->out_h;
+    a.rgb_full = job->rgb_full ? 1 : 0;
     return a;
 }
 
@@ -543,6 +581,7 @@ int ensure_quick_records(RtcScene *sc, const rtc::RenderArgs &a, int mode, bool 
     if ((!(need <= sc->q_obound) || sc->q_layout != q_layout) && sc->ntris > 0) {
         const float ob = sc->q_layout != q_layout && need <= sc->q_obound ? sc->q_obound : need * 1.25f;
         rtc::quick_records_kernel<<<(sc->ntris + 127) / 128, 128, 0, st>>>(sc->geo, sc->ntris, ob, sc->qrec, q_layout);
+        count_launch();
         CU(cudaGetLastError());
         sc->q_obound = ob;
         sc->q_layout = q_layout;
@@ -552,7 +591,7 @@ int ensure_quick_records(RtcScene *sc, const rtc::RenderArgs &a, int mode, bool 
 
 // The path kernel, pool form (rtc_pool.cuh): the default for every frame it supports.
 int launch_pool(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const float2 *rec, int planes, int mode,
-                cudaStream_t st)
+                unsigned max_tasks, cudaStream_t st)
 {
     rtc::PoolWork w;
     memset(&w, 0, sizeof w);
@@ -569,6 +608,7 @@ int launch_pool(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const f
     w.cursor = sc->counters + 1;
     w.error = sc->counters + 4;
     w.planes = planes;
+    w.max_tasks = max_tasks;
     w.spec = env_int("RTC_NO_SPEC", 0) == 0;
     w.ctx_share_div = std::max(1, env_int("RTC_POOL_SHARE_DIV", 2));
     w.tile = env_int("RTC_PATH_TILE", rtc::PATH_TILE);
@@ -611,6 +651,7 @@ int launch_pool(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const f
     const double bound = (double)tasks * (double)a.spp * (2.0 * a.maxBounce + 4.0) + 1e4;
     w.watchdog = (unsigned long long)std::min(bound, 4e7);
     kern<<<blocks, 32 * warps, smem, st>>>(a, w);
+    count_launch();
     CU(cudaGetLastError());
     return RTC_OK;
 }
@@ -631,12 +672,28 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
     const int mode = ref_quick ? 0 : ((flags & RTC_FLAG_VERIFY_QUICK) ? form + 1 : (sc->quick_ok ? form : 0));
     if (rtc::mode_verify(mode) && !a.stats)
         return fail(RTC_ERR_ARG, "RTC_FLAG_VERIFY_QUICK needs a stats buffer");
-    // the pool kernel (samples out of order, two rays per lane) for the pixels whose primary hit is known, unless the
-    // first form is asked for, the quick records are wanted one triangle at a time (RTC_QUICK_FORM=1), or a path can be
-    // longer than its 8-bit counters
-    if (list != nullptr && rec != nullptr && !(flags & RTC_FLAG_SERIAL_PATHS) && env_int("RTC_PATHS_V1", 0) == 0 &&
-        a.maxBounce <= rtc::POOL_MAX_BOUNCE && (mode == 0 || mode == 3 || mode == 4))
-        return launch_pool(sc, a, list, rec, planes, mode, st);
+    // Two forms of the path kernel.  The pool form (samples of a pixel out of order, full warps in every pass, two
+    // rays per lane) is the one for SHORT work lists -- a frame split over several GPUs, a small image, many samples on
+    // few pixels -- where the serial form runs out of pixels to keep its lanes busy; with more listed pixels than the
+    // serial form has lanes, its register-resident state and absence of scheduling code win by a few percent (C4, path
+    // kernel, one B200: 3.43 ms against 3.6 ms; on a 1/8 share 1.07 ms against 0.66 ms).  The list's length is only
+    // known on the device, so both are launched and the one the list is not meant for returns at once.
+    // RTC_PATHS=pool|serial (or RTC_FLAG_SERIAL_PATHS) forces one form.  The pool form needs the primary hits
+    // (list + rec), packed or reference-arithmetic quick tests, and paths no longer than its 8-bit counters.
+    const char *force = getenv("RTC_PATHS");
+    const bool pool_ok = list != nullptr && rec != nullptr && a.maxBounce <= rtc::POOL_MAX_BOUNCE &&
+                         (mode == 0 || mode == 3 || mode == 4);
+    const bool want_serial = (flags & RTC_FLAG_SERIAL_PATHS) != 0 || env_int("RTC_PATHS_V1", 0) != 0 ||
+                             (force && strcmp(force, "serial") == 0);
+    const bool want_pool = force && strcmp(force, "pool") == 0;
+    unsigned split_at = 0; // lists shorter than this go to the pool form
+    if (pool_ok && !want_serial) {
+        const unsigned serial_lanes = (unsigned)sc->nsm * 6u * rtc::PATH_THREADS;
+        split_at = want_pool ? 0xffffffffu : (unsigned)((unsigned long long)serial_lanes * (unsigned)std::max(0, env_int("RTC_POOL_MAX_FACTOR", 125)) / 100u);
+        int rc_p = launch_pool(sc, a, list, rec, planes, mode, split_at, st);
+        if (rc_p || want_pool)
+            return rc_p;
+    }
     w.qrec = nullptr;
     w.obound = 0.f;
     if (mode != 0) {
@@ -648,6 +705,7 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
     }
     w.list = list;
     w.rec = rec;
+    w.min_tasks = split_at;
     w.list_count = sc->counters;
     w.cursor = sc->counters + 1;
     w.planes = planes;
@@ -691,8 +749,14 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
     // RTC_GROUP_OVERSUB (percent, default 100): let the group mode count on more lanes than are resident -- groups then
     // take their pixels in more than one wave (A/B knob for frames split over 2-4 GPUs)
     w.group_lanes = (unsigned)((unsigned long long)blocks_g * rtc::PATH_THREADS * (unsigned)std::max(1, env_int("RTC_GROUP_OVERSUB", 100)) / 100u);
+    if (split_at != 0)
+        w.group_lanes = 0; // short lists are the pool form's: the serial form's group mode is not needed
     kern<<<blocks, rtc::PATH_THREADS, smem, st>>>(a, w);
-    kern_groups<<<blocks_g, rtc::PATH_THREADS, smem, st>>>(a, w);
+    count_launch();
+    if (split_at == 0) {
+        kern_groups<<<blocks_g, rtc::PATH_THREADS, smem, st>>>(a, w);
+        count_launch();
+    }
     CU(cudaGetLastError());
     return RTC_OK;
 }
@@ -751,6 +815,56 @@ int planes_of(const RtcDeviceJob *job)
 } // namespace
 
 extern "C" {
+
+uint64_t rtc_launches_total(void) { return g_launches.load(); }
+
+int rtc_ipc_export(int device, const void *d_ptr, unsigned char handle[RTC_IPC_HANDLE_BYTES])
+{
+    static_assert(sizeof(cudaIpcMemHandle_t) == RTC_IPC_HANDLE_BYTES, "CUDA IPC handles are 64 bytes");
+    if (!d_ptr || !handle)
+        return fail(RTC_ERR_ARG, "ipc_export: NULL argument");
+    CU(cudaSetDevice(device));
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, const_cast<void *>(d_ptr)));
+    memcpy(handle, &h, sizeof h);
+    return RTC_OK;
+}
+
+int rtc_ipc_open(int device, const unsigned char handle[RTC_IPC_HANDLE_BYTES], void **d_ptr)
+{
+    if (!d_ptr || !handle)
+        return fail(RTC_ERR_ARG, "ipc_open: NULL argument");
+    CU(cudaSetDevice(device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof h);
+    CU(cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return RTC_OK;
+}
+
+int rtc_ipc_close(int device, void *d_ptr)
+{
+    if (!d_ptr)
+        return RTC_OK;
+    CU(cudaSetDevice(device));
+    CU(cudaIpcCloseMemHandle(d_ptr));
+    return RTC_OK;
+}
+
+int rtc_enable_peer(int device, int peer)
+{
+    if (device == peer)
+        return RTC_OK;
+    int ok = 0;
+    CU(cudaDeviceCanAccessPeer(&ok, device, peer));
+    if (!ok)
+        return fail(RTC_ERR_CUDA, "device %d cannot access device %d's memory", device, peer);
+    CU(cudaSetDevice(device));
+    cudaError_t e = cudaDeviceEnablePeerAccess(peer, 0);
+    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+        return fail(RTC_ERR_CUDA, "cudaDeviceEnablePeerAccess(%d -> %d): %s", device, peer, cudaGetErrorString(e));
+    cudaGetLastError();
+    return RTC_OK;
+}
 
 int rtc_render_launch_count(const RtcScene *sc, const RtcDeviceJob *job, int want_ids)
 {
@@ -844,6 +958,7 @@ static int render_device_impl(const RtcScene *sc, const Scene *sky, const Camera
         rtc::PrimaryFrame fr = make_primary_frame(cam, job, R, block);
         if (sc->ntris > 0) {
             rtc::prepare_primary_kernel<<<(sc->ntris + 127) / 128, 128, 0, st>>>(a.sc, fr, msc->tab);
+            count_launch();
             CU(cudaGetLastError());
         }
         if (block && nsph_eff > 0) {
@@ -854,6 +969,7 @@ static int render_device_impl(const RtcScene *sc, const Scene *sky, const Camera
                 msc->cap_sphq = nsph_eff;
             }
             rtc::prepare_spheres_kernel<<<(nsph_eff + 31) / 32, 32, 0, st>>>(a.sc, fr, msc->sphq);
+            count_launch();
             CU(cudaGetLastError());
         }
         rtc::SkyWork sw;
@@ -869,6 +985,7 @@ static int render_device_impl(const RtcScene *sc, const Scene *sky, const Camera
         if (sw.tile < 1 || sw.tile > rtc::SKY_TILE)
             sw.tile = rtc::SKY_TILE;
         sw.stream = (env_int("RTC_FORCE_STREAM", 0) != 0 || sc->ntris > rtc::SKY_TILE) ? 1 : 0;
+        sw.segs = 1;
         if (block) {
             size_t bsmem = rtc::skyblock_smem_bytes(sc->ntris, sw.stream != 0);
             dim3 bgrid((job->out_w + 8 * rtc::BLK_W - 1) / (8 * rtc::BLK_W),
@@ -877,12 +994,26 @@ static int render_device_impl(const RtcScene *sc, const Scene *sky, const Camera
             if ((rc = kernel_occupancy(sc->device, reinterpret_cast<const void *>(rtc::render_skyblock_kernel),
                                        rtc::SKYB_THREADS, bsmem, &sky_per_sm)))
                 return rc;
+            {
+                // a short pixel grid (a frame split over several GPUs) leaves SMs idle while one warp re-sweeps its region
+                // once per sample: split the samples over CTAs until the grid covers the machine twice
+                const long long ctas = (long long)bgrid.x * bgrid.y * planes;
+                const long long room = 2ll * msc->nsm * std::max(1, sky_per_sm);
+                const int min_samples = std::max(1, job->spp / (job->nsplit > 1 ? job->nsplit : 1));
+                int segs = (int)std::min<long long>(std::max<long long>(1, room / std::max<long long>(1, ctas)), 16);
+                segs = std::max(1, std::min(segs, min_samples / 4));
+                if (getenv("RTC_SKY_SEGS")) // tests / A-B: any count that leaves every segment of every sub-stream a sample
+                    segs = std::max(1, std::min(std::min(env_int("RTC_SKY_SEGS", 1), 64), min_samples));
+                sw.segs = segs;
+                bgrid.z = (unsigned)(planes * segs);
+            }
             if (msc->prog && job->nsplit <= 1 && d_rgb) {
                 a.prog = msc->prog;
                 a.prog_rows = msc->prog_rows;
                 a.prog_chunks = msc->prog_chunks;
             }
             rtc::render_skyblock_kernel<<<bgrid, rtc::SKYB_THREADS, bsmem, st>>>(a, msc->tab, sw);
+            count_launch();
             CU(cudaGetLastError());
             if (a.prog) { // sky pixels are final; hit pixels follow chunk by chunk from the path kernel
                 CU(cudaEventRecord(msc->sky_ev, st));
@@ -919,6 +1050,7 @@ static int render_device_impl(const RtcScene *sc, const Scene *sky, const Camera
                     CU(cudaStreamWaitEvent(msc->aux, msc->fork_ev, 0));
                 }
                 rtc::render_blocktask_kernel<<<msc->nsm * per_sm, rtc::BTASK_THREADS, tsmem, ts>>>(a, msc->tab, tw);
+                count_launch();
                 CU(cudaGetLastError());
                 if (overlap)
                     CU(cudaEventRecord(msc->join_ev, msc->aux));
@@ -940,6 +1072,7 @@ static int render_device_impl(const RtcScene *sc, const Scene *sky, const Camera
         CU(cudaFuncSetAttribute(rtc::render_sky_kernel<RR>, cudaFuncAttributeMaxDynamicSharedMemorySize,         \
                                 (int)smem));                                                                    \
         rtc::render_sky_kernel<RR><<<fgrid, rtc::FAST_THREADS, smem, st>>>(a, msc->tab, sw);                     \
+        count_launch(); \
     } while (0)
         if (R == 16)
             LAUNCH_SKY(16);
@@ -972,6 +1105,7 @@ static int render_device_impl(const RtcScene *sc, const Scene *sky, const Camera
         rtc::render_kernel<true><<<grid, rtc::CTA_THREADS, 0, st>>>(a);
     else
         rtc::render_kernel<false><<<grid, rtc::CTA_THREADS, 0, st>>>(a);
+    count_launch();
     CU(cudaGetLastError());
     return RTC_OK;
 }
@@ -1002,6 +1136,7 @@ int rtc_sum_quantize_device(int device, const float *d_planes, int nplanes, size
     CU(cudaSetDevice(device));
     rtc::sum_quantize_kernel<<<(unsigned)((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
         d_planes, nplanes, n, d_rgb, d_sum);
+    count_launch();
     CU(cudaGetLastError());
     return RTC_OK;
 }
@@ -1080,6 +1215,7 @@ struct DeviceSlot {
     // single-GPU frames: the image goes to the host in row chunks, each as soon as its pixels are final
     cudaStream_t copy = nullptr;
     unsigned *prog = nullptr; // 3 * COPY_CHUNKS words, see RenderArgs::prog
+    unsigned long long *h_stats = nullptr; // page-locked: the counters arrive with the frame, no extra blocking copy
 };
 
 constexpr int COPY_CHUNKS = 16;
@@ -1121,6 +1257,8 @@ int slot_init(DeviceSlot &s, int dev)
             CU(cudaEventCreate(&e));
     if (!s.stats)
         CU(cudaMalloc(&s.stats, sizeof(unsigned long long) * RTC_DEVICE_STATS_WORDS));
+    if (!s.h_stats)
+        CU(cudaMallocHost(&s.h_stats, sizeof(unsigned long long) * RTC_DEVICE_STATS_WORDS));
     return RTC_OK;
 }
 
@@ -1154,9 +1292,14 @@ __global__ void uninterleave_kernel(const T *__restrict__ all, T *__restrict__ i
 
 } // namespace
 
+namespace {
+void stop_device_workers();
+}
+
 extern "C" void render_cuda_shutdown(void)
 {
     std::lock_guard<std::mutex> lk(g_ctx.mu);
+    stop_device_workers();
     for (int i = 0; i < g_ctx.ncomms; ++i)
         g_ctx.nccl.CommDestroy(g_ctx.comms[i]);
     g_ctx.ncomms = 0;
@@ -1177,6 +1320,7 @@ extern "C" void render_cuda_shutdown(void)
         cudaFree(s.img);
         cudaFree(s.accum);
         cudaFree(s.prog);
+        cudaFreeHost(s.h_stats);
         if (s.copy)
             cudaStreamDestroy(s.copy);
         s = DeviceSlot();
@@ -1209,222 +1353,376 @@ int ensure_comms(int G)
     return RTC_OK;
 }
 
+// One call of render_cuda: what every device's share looks like.
+struct Call {
+    const Scene *scene;
+    const Camera *cam;
+    uint8_t *out_rgb;
+    const RenderParams *p;
+    int W, H, G, S, base;
+    bool samples;   // sample split (sub-stream planes gathered and summed on device 0)
+    bool direct;    // tile split, G > 1: every device copies its own bands into the caller's image
+    bool pipelined; // G == 1: row chunks go to the host as soon as their pixels are final
+    size_t img_bytes, part_bytes;
+    int chunk_rows;
+    RtcDeviceJob job[MAX_GPUS];
+};
+
+struct DevResult {
+    int rc = RTC_OK;
+    char err[512] = "";
+    unsigned long long h[RTC_DEVICE_STATS_WORDS] = {0};
+    float up_ms = 0, k_ms = 0;
+    bool touched = false; // asynchronous work of this call may be in flight on the device's streams
+};
+
+// Everything device g does for the frame, queued asynchronously: upload + flatten, render, and -- unless a collective
+// follows (NCCL modes) -- the copy of its pixels into the caller's image.
+int device_enqueue(const Call &c, int g, DevResult &r)
+{
+    const RenderParams *p = c.p;
+    const int dev = c.base + g;
+    DeviceSlot &s = g_ctx.slot[dev];
+    int rc = slot_init(s, dev);
+    if (rc)
+        return rc;
+    const bool gather = c.G > 1 && !c.direct;
+    if ((rc = ensure(&s.all, &s.all_bytes, gather ? c.part_bytes * c.G : c.part_bytes)))
+        return rc;
+    s.part = static_cast<char *>(s.all) + (gather ? c.part_bytes * g : 0);
+    const size_t npix = (size_t)c.job[g].out_w * c.job[g].out_h;
+    const bool want_ids = p->out_primary_id && (!c.samples || g == 0);
+    if (want_ids)
+        if ((rc = ensure(reinterpret_cast<void **>(&s.ids), &s.ids_bytes, npix * sizeof(int32_t))))
+            return rc;
+    if (!c.samples && c.S > 1)
+        if ((rc = ensure(reinterpret_cast<void **>(&s.accum), &s.accum_bytes, (size_t)c.S * npix * 3 * sizeof(float))))
+            return rc;
+    if (g == 0 && gather)
+        if ((rc = ensure(reinterpret_cast<void **>(&s.img), &s.img_bytes, c.img_bytes)))
+            return rc;
+    r.touched = true;
+    if (c.pipelined) {
+        if (!s.copy)
+            CU(cudaStreamCreateWithFlags(&s.copy, cudaStreamNonBlocking));
+        if (!s.prog)
+            CU(cudaMalloc(&s.prog, sizeof(unsigned) * 3 * COPY_CHUNKS));
+        if (!s.scene->sky_ev)
+            CU(cudaEventCreateWithFlags(&s.scene->sky_ev, cudaEventDisableTiming));
+        CU(cudaMemsetAsync(s.prog, 0, sizeof(unsigned) * 3 * COPY_CHUNKS, s.stream));
+        s.scene->prog = s.prog;
+        s.scene->prog_rows = c.chunk_rows;
+        s.scene->prog_chunks = COPY_CHUNKS;
+    }
+    CU(cudaEventRecord(s.ev[0], s.stream));
+    CU(cudaMemsetAsync(s.stats, 0, sizeof(unsigned long long) * RTC_DEVICE_STATS_WORDS, s.stream));
+    if ((rc = scene_upload(s.scene, p->tris, p->ntris, p->spheres, p->nspheres, s.stream)))
+        return rc;
+    CU(cudaEventRecord(s.ev[1], s.stream));
+    int32_t *d_ids = want_ids ? s.ids : nullptr;
+    uint64_t *d_stats = reinterpret_cast<uint64_t *>(s.stats);
+    if (c.samples) {
+        rc = rtc_render_device(s.scene, c.scene, c.cam, &c.job[g], nullptr, static_cast<float *>(s.part), d_ids, d_stats, s.stream);
+    } else if (c.S > 1) {
+        rc = rtc_render_device(s.scene, c.scene, c.cam, &c.job[g], nullptr, s.accum, d_ids, d_stats, s.stream);
+        if (!rc)
+            rc = rtc_sum_quantize_device(dev, s.accum, c.S, npix * 3, static_cast<uint8_t *>(s.part), nullptr, s.stream);
+    } else {
+        rc = rtc_render_device(s.scene, c.scene, c.cam, &c.job[g], static_cast<uint8_t *>(s.part), nullptr, d_ids, d_stats, s.stream);
+    }
+    if (rc)
+        return rc;
+    CU(cudaSetDevice(dev));
+    CU(cudaEventRecord(s.ev[2], s.stream));
+    // the counters travel with the frame (page-locked buffer): no blocking copy after the synchronisation
+    CU(cudaMemcpyAsync(s.h_stats, s.stats, sizeof(unsigned long long) * RTC_DEVICE_STATS_WORDS, cudaMemcpyDeviceToHost, s.stream));
+    if (c.direct) {
+        if ((rc = rtc_download_bands(dev, s.part, c.out_rgb, (size_t)c.W * 3, c.H, c.G, BAND_H, g, s.stream)))
+            return rc;
+    } else if (c.G == 1) {
+        const uint8_t *d_final = static_cast<const uint8_t *>(s.part);
+        if (c.pipelined) {
+            // the copy stream follows the kernels: sky pixels are final after the classification kernel, the rows of
+            // a chunk once the path kernel has finished its last primary-hit pixel (flag set on the device;
+            // rtc_render_device sets every flag at the end of the frame whatever path it took)
+            CU(cudaStreamWaitEvent(s.copy, s.scene->sky_ev, 0));
+            for (int k = 0; k < COPY_CHUNKS; ++k) {
+                const size_t r0 = (size_t)k * c.chunk_rows;
+                if (r0 >= (size_t)c.H)
+                    break;
+                const size_t r1 = std::min<size_t>((size_t)c.H, r0 + c.chunk_rows);
+                if (wait_value32()(s.copy, (unsigned long long)(uintptr_t)(s.prog + 2 * COPY_CHUNKS + k), 1u, 0u /* GEQ */) != 0)
+                    return fail(RTC_ERR_CUDA, "cuStreamWaitValue32 failed");
+                CU(cudaMemcpyAsync(c.out_rgb + r0 * c.W * 3, d_final + r0 * c.W * 3, (r1 - r0) * c.W * 3, cudaMemcpyDeviceToHost, s.copy));
+            }
+        } else {
+            CU(cudaMemcpyAsync(c.out_rgb, d_final, c.img_bytes, cudaMemcpyDeviceToHost, s.stream));
+        }
+    }
+    return RTC_OK;
+}
+
+// wait for device g's queued work whatever happened before (a blocking call must not return with copies into the
+// caller's buffers still in flight), and disarm the one-shot chunk flags
+void device_drain(const Call &c, int g)
+{
+    DeviceSlot &s = g_ctx.slot[c.base + g];
+    cudaSetDevice(c.base + g);
+    if (s.stream)
+        cudaStreamSynchronize(s.stream);
+    if (s.copy)
+        cudaStreamSynchronize(s.copy);
+    if (s.scene)
+        s.scene->prog = nullptr;
+    cudaGetLastError();
+}
+
+// after the frame: counters, event times, primary-hit ids of device g
+int device_finish(const Call &c, int g, DevResult &r)
+{
+    const RenderParams *p = c.p;
+    const int dev = c.base + g;
+    DeviceSlot &s = g_ctx.slot[dev];
+    CU(cudaSetDevice(dev));
+    CU(cudaStreamSynchronize(s.stream));
+    if (c.pipelined)
+        CU(cudaStreamSynchronize(s.copy));
+    memcpy(r.h, s.h_stats, sizeof r.h);
+    CU(cudaEventElapsedTime(&r.up_ms, s.ev[0], s.ev[1]));
+    CU(cudaEventElapsedTime(&r.k_ms, s.ev[1], s.ev[2]));
+    if (p->out_primary_id && (!c.samples || g == 0)) {
+        const size_t npix = (size_t)c.job[g].out_w * c.job[g].out_h;
+        if (c.G == 1 || c.samples) {
+            CU(cudaMemcpy(p->out_primary_id, s.ids, npix * sizeof(int32_t), cudaMemcpyDeviceToHost));
+        } else { // this device's bands of the id map (rows of different devices are disjoint)
+            std::vector<int32_t> tmp(npix);
+            CU(cudaMemcpy(tmp.data(), s.ids, npix * sizeof(int32_t), cudaMemcpyDeviceToHost));
+            for (int j = 0; j < c.job[g].out_h; ++j) {
+                const int y = c.job[g].subset.row_start + (j / BAND_H) * c.job[g].subset.row_step + j % BAND_H;
+                memcpy(p->out_primary_id + (size_t)y * c.W, tmp.data() + (size_t)j * c.W, sizeof(int32_t) * c.W);
+            }
+        }
+    }
+    return RTC_OK;
+}
+
+// ---- one host thread per device (render_cuda with ngpus > 1): the devices' launch sequences, copies and
+//      synchronisations run side by side instead of one after the other on the caller's thread ----
+class DeviceWorkers {
+  public:
+    void run(int n, const std::function<void(int)> &fn) // fn(1) .. fn(n - 1) on workers, fn(0) on the caller; waits for all
+    {
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            while ((int)threads_.size() < n - 1) {
+                const int id = (int)threads_.size() + 1;
+                threads_.emplace_back([this, id] { loop(id); });
+            }
+            fn_ = &fn;
+            pending_ = n - 1;
+            active_ = n;
+            ++epoch_;
+        }
+        cv_.notify_all();
+        fn(0);
+        std::unique_lock<std::mutex> lk(mu_);
+        done_.wait(lk, [this] { return pending_ == 0; });
+        fn_ = nullptr;
+    }
+    void stop()
+    {
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            quit_ = true;
+        }
+        cv_.notify_all();
+        for (auto &t : threads_)
+            t.join();
+        threads_.clear();
+        quit_ = false;
+    }
+
+  private:
+    void loop(int id)
+    {
+        unsigned long long seen = 0;
+        while (true) {
+            const std::function<void(int)> *fn = nullptr;
+            {
+                std::unique_lock<std::mutex> lk(mu_);
+                cv_.wait(lk, [&] { return quit_ || (epoch_ != seen && id < active_); });
+                if (quit_)
+                    return;
+                seen = epoch_;
+                fn = fn_;
+            }
+            (*fn)(id);
+            {
+                std::lock_guard<std::mutex> lk(mu_);
+                --pending_;
+            }
+            done_.notify_one();
+        }
+    }
+    std::mutex mu_;
+    std::condition_variable cv_, done_;
+    std::vector<std::thread> threads_;
+    const std::function<void(int)> *fn_ = nullptr;
+    unsigned long long epoch_ = 0;
+    int pending_ = 0, active_ = 0;
+    bool quit_ = false;
+} g_workers;
+
+void stop_device_workers() { g_workers.stop(); }
+
 int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const RenderParams *p)
 {
-    const int W = p->width, H = p->height;
-    int G = p->ngpus > 1 ? p->ngpus : 1;
+    Call c;
+    c.scene = scene;
+    c.cam = cam;
+    c.out_rgb = out_rgb;
+    c.p = p;
+    c.W = p->width;
+    c.H = p->height;
+    c.G = p->ngpus > 1 ? p->ngpus : 1;
+    c.base = 0;
+    const unsigned long long launches0 = g_launches.load();
+    const int W = c.W, H = c.H, G = c.G;
     const bool trace = getenv("RTC_TRACE") != nullptr;
     const auto t_entry = std::chrono::steady_clock::now();
     auto since = [&]() { return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_entry).count(); };
-    double t_enq = 0, t_sync = 0;
     int ndev = rtc_device_count();
     if (ndev <= 0)
         return fail(RTC_ERR_NO_GPU, "no CUDA device: librtc_b200 has no CPU fallback");
     if (G > ndev || G > MAX_GPUS)
         return fail(RTC_ERR_NO_GPU, "ngpus = %d but %d device(s) visible", G, ndev);
-    int base = 0;
     if (G == 1) {
         const char *e = getenv("RTC_DEVICE");
         if (e)
-            base = atoi(e);
-        if (base < 0 || base >= ndev)
-            return fail(RTC_ERR_NO_GPU, "RTC_DEVICE=%d but %d device(s) visible", base, ndev);
+            c.base = atoi(e);
+        if (c.base < 0 || c.base >= ndev)
+            return fail(RTC_ERR_NO_GPU, "RTC_DEVICE=%d but %d device(s) visible", c.base, ndev);
     }
-    const bool samples = G > 1 && p->split_mode == RTC_SPLIT_SAMPLES;
-    int S = p->nsplit > 1 ? p->nsplit : 1;
-    if (samples) {
+    c.samples = G > 1 && p->split_mode == RTC_SPLIT_SAMPLES;
+    c.S = p->nsplit > 1 ? p->nsplit : 1;
+    if (c.samples) {
+        // sub-stream seeds x + y*W + g*W*H are this library's own definition (not the reference's one stream per pixel):
+        // the caller has to ask for them, so that the image never silently depends on the GPU count
         if (p->nsplit <= 1)
-            S = G;
-        if (S % G)
-            return fail(RTC_ERR_ARG, "sample split: nsplit (%d) must be a multiple of ngpus (%d)", S, G);
+            return fail(RTC_ERR_ARG, "sample split: set nsplit (sub-streams per pixel, a multiple of ngpus = %d); only the tile "
+                                     "split reproduces the reference's image", G);
+        if (c.S % G)
+            return fail(RTC_ERR_ARG, "sample split: nsplit (%d) must be a multiple of ngpus (%d)", c.S, G);
     }
     // Tile split: the caller's image is in HOST memory, so every device copies its own bands straight to their rows
     // (rtc_download_bands: one strided copy per device, each over its own PCIe link) -- no gather through device 0.
     // RTC_GATHER=1 keeps the frame's assembly on device 0 (NCCL all-gather over NVLink + un-interleave + one copy);
     // the sample split always needs it (ordered sum of the sub-stream planes).
-    const bool direct = G > 1 && !samples && env_int("RTC_GATHER", 0) == 0;
-    if (G > 1 && !direct) {
+    c.direct = G > 1 && !c.samples && env_int("RTC_GATHER", 0) == 0;
+    const bool gather = G > 1 && !c.direct;
+    if (gather) {
         int rc = ensure_comms(G);
         if (rc)
             return rc;
     }
-    const size_t img_bytes = (size_t)W * H * 3;
-
-    // per-device jobs
-    RtcDeviceJob job[MAX_GPUS];
-    size_t part_bytes = 0; // gather slice per device
+    c.img_bytes = (size_t)W * H * 3;
     for (int g = 0; g < G; ++g) {
-        RtcDeviceJob &j = job[g];
+        RtcDeviceJob &j = c.job[g];
         memset(&j, 0, sizeof j);
         j.width = W; j.height = H; j.spp = p->spp; j.maxBounce = p->maxBounce; j.trianglesOnly = p->trianglesOnly;
-        j.nsplit = S;
+        j.nsplit = c.S;
         j.flags = p->flags;
-        if (samples) {
-            j.split_first = g * (S / G);
-            j.split_count = S / G;
+        if (c.samples) {
+            j.split_first = g * (c.S / G);
+            j.split_count = c.S / G;
             j.subset = RtcSubset{0, 1, 0, 1, 1};
         } else {
             j.split_first = 0;
-            j.split_count = S;
+            j.split_count = c.S;
             j.subset = G > 1 ? RtcSubset{g * BAND_H, G * BAND_H, 0, 1, BAND_H} : RtcSubset{0, 1, 0, 1, 1};
         }
         rtc_subset_size(W, H, &j.subset, &j.out_w, &j.out_h);
     }
-    if (samples)
-        part_bytes = (size_t)(S / G) * img_bytes * sizeof(float);
-    else
-        part_bytes = (size_t)job[0].out_h * W * 3; // device 0 owns the most rows
+    c.part_bytes = c.samples ? (size_t)(c.S / G) * c.img_bytes * sizeof(float) : (size_t)c.job[0].out_h * W * 3; // device 0 owns the most rows
+    // one GPU, plain frame: the device->host copy runs chunk by chunk on its own stream, behind the kernels
+    // (only frames whose copy takes long enough to be worth 2 x COPY_CHUNKS more runtime calls)
+    c.pipelined = G == 1 && c.S == 1 && H >= 8 * COPY_CHUNKS && c.img_bytes >= (size_t)env_int("RTC_PIPELINE_MIN_BYTES", 4 << 20) &&
+                  wait_value32() != nullptr && getenv("RTC_NO_PIPELINE") == nullptr;
+    c.chunk_rows = ((H + COPY_CHUNKS - 1) / COPY_CHUNKS + 7) / 8 * 8; // whole 8 x 4 pixel blocks
 
-    bool pipelined = false;
-    int chunk_rows = 0;
-    // launch everything, device by device (all asynchronous)
-    for (int g = 0; g < G; ++g) {
-        int dev = base + g;
-        DeviceSlot &s = g_ctx.slot[dev];
-        int rc = slot_init(s, dev);
-        if (rc)
-            return rc;
-        if ((rc = ensure(&s.all, &s.all_bytes, part_bytes * G)))
-            return rc;
-        s.part = static_cast<char *>(s.all) + part_bytes * g;
-        size_t npix = (size_t)job[g].out_w * job[g].out_h;
-        if (p->out_primary_id && (!samples || g == 0))
-            if ((rc = ensure(reinterpret_cast<void **>(&s.ids), &s.ids_bytes, npix * sizeof(int32_t))))
-                return rc;
-        if (!samples && S > 1)
-            if ((rc = ensure(reinterpret_cast<void **>(&s.accum), &s.accum_bytes, (size_t)S * npix * 3 * sizeof(float))))
-                return rc;
-        if (g == 0 && G > 1)
-            if ((rc = ensure(reinterpret_cast<void **>(&s.img), &s.img_bytes, img_bytes)))
-                return rc;
-        // one GPU, plain frame: the device->host copy runs chunk by chunk on its own stream, behind the kernels
-        // (only frames whose copy takes long enough to be worth 2 x COPY_CHUNKS more runtime calls)
-        pipelined = G == 1 && S == 1 && !samples && H >= 8 * COPY_CHUNKS && img_bytes >= (size_t)env_int("RTC_PIPELINE_MIN_BYTES", 4 << 20) &&
-                    wait_value32() != nullptr && getenv("RTC_NO_PIPELINE") == nullptr;
-        if (pipelined) {
-            if (!s.copy)
-                CU(cudaStreamCreateWithFlags(&s.copy, cudaStreamNonBlocking));
-            if (!s.prog)
-                CU(cudaMalloc(&s.prog, sizeof(unsigned) * 3 * COPY_CHUNKS));
-            if (!s.scene->sky_ev)
-                CU(cudaEventCreateWithFlags(&s.scene->sky_ev, cudaEventDisableTiming));
-            CU(cudaMemsetAsync(s.prog, 0, sizeof(unsigned) * 3 * COPY_CHUNKS, s.stream));
-            chunk_rows = ((H + COPY_CHUNKS - 1) / COPY_CHUNKS + 7) / 8 * 8; // whole 8 x 4 pixel blocks
-            s.scene->prog = s.prog;
-            s.scene->prog_rows = chunk_rows;
-            s.scene->prog_chunks = COPY_CHUNKS;
-        }
-        CU(cudaEventRecord(s.ev[0], s.stream));
-        CU(cudaMemsetAsync(s.stats, 0, sizeof(unsigned long long) * RTC_DEVICE_STATS_WORDS, s.stream));
-        if ((rc = scene_upload(s.scene, p->tris, p->ntris, p->spheres, p->nspheres, s.stream)))
-            return rc;
-        CU(cudaEventRecord(s.ev[1], s.stream));
-        int32_t *d_ids = (p->out_primary_id && (!samples || g == 0)) ? s.ids : nullptr;
-        if (samples) {
-            rc = rtc_render_device(s.scene, scene, cam, &job[g], nullptr, static_cast<float *>(s.part), d_ids,
-                                   reinterpret_cast<uint64_t *>(s.stats), s.stream);
-        } else if (S > 1) {
-            rc = rtc_render_device(s.scene, scene, cam, &job[g], nullptr, s.accum, d_ids,
-                                   reinterpret_cast<uint64_t *>(s.stats), s.stream);
-            if (!rc)
-                rc = rtc_sum_quantize_device(dev, s.accum, S, npix * 3, static_cast<uint8_t *>(s.part), nullptr,
-                                             s.stream);
-        } else {
-            rc = rtc_render_device(s.scene, scene, cam, &job[g], static_cast<uint8_t *>(s.part), nullptr, d_ids,
-                                   reinterpret_cast<uint64_t *>(s.stats), s.stream);
-        }
-        if (rc)
-            return rc;
-        CU(cudaSetDevice(dev));
-        CU(cudaEventRecord(s.ev[2], s.stream));
-    }
-
-    // gather over NVLink + finish on device 0
-    DeviceSlot &s0 = g_ctx.slot[base];
-    const uint8_t *d_final = static_cast<const uint8_t *>(s0.part);
-    if (G > 1 && !direct) {
-        NC(g_ctx.nccl.GroupStart());
-        for (int g = 0; g < G; ++g) {
-            DeviceSlot &s = g_ctx.slot[g];
-            NC(g_ctx.nccl.AllGather(s.part, s.all, part_bytes, ncclUint8, g_ctx.comms[g], s.stream));
-        }
-        NC(g_ctx.nccl.GroupEnd());
-        CU(cudaSetDevice(base));
-        if (samples) {
-            int rc = rtc_sum_quantize_device(base, static_cast<const float *>(s0.all), S, img_bytes, s0.img, nullptr,
-                                             s0.stream);
-            if (rc)
-                return rc;
-        } else {
-            uninterleave_kernel<uint8_t><<<(unsigned)((img_bytes + 255) / 256), 256, 0, s0.stream>>>(
-                static_cast<const uint8_t *>(s0.all), s0.img, W * 3, H, G, BAND_H, part_bytes);
-            CU(cudaGetLastError());
-        }
-        d_final = s0.img;
-    }
-    CU(cudaSetDevice(base));
-    CU(cudaEventRecord(s0.ev[3], s0.stream));
-    if (direct) {
-        for (int g = 0; g < G; ++g) {
-            DeviceSlot &s = g_ctx.slot[base + g];
-            int rc = rtc_download_bands(base + g, s.part, out_rgb, (size_t)W * 3, H, G, BAND_H, g, s.stream);
-            if (rc)
-                return rc;
-        }
-        CU(cudaSetDevice(base));
-    } else if (pipelined) {
-        // the copy stream follows the kernels: sky pixels are final after the classification kernel, the rows of
-        // a chunk once the path kernel has finished its last primary-hit pixel (flag set on the device;
-        // rtc_render_device sets every flag at the end of the frame whatever path it took)
-        CU(cudaStreamWaitEvent(s0.copy, s0.scene->sky_ev, 0));
-        for (int c = 0; c < COPY_CHUNKS; ++c) {
-            const size_t r0 = (size_t)c * chunk_rows;
-            if (r0 >= (size_t)H)
-                break;
-            const size_t r1 = std::min<size_t>((size_t)H, r0 + chunk_rows);
-            if (wait_value32()(s0.copy, (unsigned long long)(uintptr_t)(s0.prog + 2 * COPY_CHUNKS + c), 1u, 0u /* GEQ */) != 0)
-                return fail(RTC_ERR_CUDA, "cuStreamWaitValue32 failed");
-            CU(cudaMemcpyAsync(out_rgb + r0 * W * 3, d_final + r0 * W * 3, (r1 - r0) * W * 3, cudaMemcpyDeviceToHost, s0.copy));
-        }
+    DevResult res[MAX_GPUS];
+    int rc = RTC_OK;
+    double t_enq = 0;
+    float gather_ms = 0;
+    if (c.direct && env_int("RTC_NO_THREADS", 0) == 0) {
+        // every device on its own host thread: enqueue, copy, synchronise, read the counters
+        const std::function<void(int)> work = [&](int g) {
+            DevResult &r = res[g];
+            r.rc = device_enqueue(c, g, r);
+            if (!r.rc)
+                r.rc = device_finish(c, g, r);
+            if (r.rc)
+                snprintf(r.err, sizeof r.err, "%s", g_err);
+        };
+        g_workers.run(G, work);
+        t_enq = since();
     } else {
-        CU(cudaMemcpyAsync(out_rgb, d_final, img_bytes, cudaMemcpyDeviceToHost, s0.stream));
+        for (int g = 0; g < G && !rc; ++g)
+            rc = device_enqueue(c, g, res[g]);
+        DeviceSlot &s0 = g_ctx.slot[c.base];
+        if (!rc && gather) {
+            // gather over NVLink + finish on device 0, then one copy to the host
+            rc = [&]() -> int {
+                NC(g_ctx.nccl.GroupStart());
+                for (int g = 0; g < G; ++g) {
+                    DeviceSlot &s = g_ctx.slot[g];
+                    NC(g_ctx.nccl.AllGather(s.part, s.all, c.part_bytes, ncclUint8, g_ctx.comms[g], s.stream));
+                }
+                NC(g_ctx.nccl.GroupEnd());
+                CU(cudaSetDevice(c.base));
+                if (c.samples) {
+                    int r2 = rtc_sum_quantize_device(c.base, static_cast<const float *>(s0.all), c.S, c.img_bytes, s0.img, nullptr, s0.stream);
+                    if (r2)
+                        return r2;
+                } else {
+                    uninterleave_kernel<uint8_t><<<(unsigned)((c.img_bytes + 255) / 256), 256, 0, s0.stream>>>(
+                        static_cast<const uint8_t *>(s0.all), s0.img, W * 3, H, G, BAND_H, c.part_bytes);
+                    count_launch();
+                    CU(cudaGetLastError());
+                }
+                CU(cudaEventRecord(s0.ev[3], s0.stream));
+                CU(cudaMemcpyAsync(out_rgb, s0.img, c.img_bytes, cudaMemcpyDeviceToHost, s0.stream));
+                return RTC_OK;
+            }();
+        }
+        t_enq = since();
+        for (int g = 0; g < G && !rc; ++g)
+            rc = device_finish(c, g, res[g]);
+        if (!rc && gather) {
+            CU(cudaSetDevice(c.base));
+            cudaEventElapsedTime(&gather_ms, s0.ev[2], s0.ev[3]);
+        }
     }
+    for (int g = 0; g < G; ++g)
+        if (res[g].rc && !rc) {
+            rc = res[g].rc;
+            snprintf(g_err, sizeof g_err, "%s", res[g].err);
+        }
+    if (rc) {
+        for (int g = 0; g < G; ++g)
+            if (res[g].touched)
+                device_drain(c, g);
+        return rc;
+    }
+    const double t_sync = since();
 
-    t_enq = since();
-    // ids and counters
-    std::vector<int32_t> tmp;
     unsigned long long tot[RTC_DEVICE_STATS_WORDS] = {0};
     float up_ms = 0, k_ms = 0;
     for (int g = 0; g < G; ++g) {
-        int dev = base + g;
-        DeviceSlot &s = g_ctx.slot[dev];
-        CU(cudaSetDevice(dev));
-        CU(cudaStreamSynchronize(s.stream));
-        if (pipelined)
-            CU(cudaStreamSynchronize(s.copy));
-        t_sync = since();
-        unsigned long long h[RTC_DEVICE_STATS_WORDS];
-        CU(cudaMemcpy(h, s.stats, sizeof h, cudaMemcpyDeviceToHost));
         for (int i = 0; i < RTC_DEVICE_STATS_WORDS; ++i)
-            tot[i] += h[i];
-        float a = 0, b = 0;
-        CU(cudaEventElapsedTime(&a, s.ev[0], s.ev[1]));
-        CU(cudaEventElapsedTime(&b, s.ev[1], s.ev[2]));
-        up_ms = a > up_ms ? a : up_ms;
-        k_ms = b > k_ms ? b : k_ms;
-        if (p->out_primary_id && (!samples || g == 0)) {
-            size_t npix = (size_t)job[g].out_w * job[g].out_h;
-            if (G == 1 || samples) {
-                CU(cudaMemcpy(p->out_primary_id, s.ids, npix * sizeof(int32_t), cudaMemcpyDeviceToHost));
-            } else {
-                tmp.resize(npix);
-                CU(cudaMemcpy(tmp.data(), s.ids, npix * sizeof(int32_t), cudaMemcpyDeviceToHost));
-                for (int j = 0; j < job[g].out_h; ++j) {
-                    int y = job[g].subset.row_start + (j / BAND_H) * job[g].subset.row_step + j % BAND_H;
-                    memcpy(p->out_primary_id + (size_t)y * W, tmp.data() + (size_t)j * W, sizeof(int32_t) * W);
-                }
-            }
-        }
+            tot[i] += res[g].h[i];
+        up_ms = std::max(up_ms, res[g].up_ms);
+        k_ms = std::max(k_ms, res[g].k_ms);
     }
     if (tot[rtc::ST_MISMATCH] >> 40)
         return fail(RTC_ERR_CUDA, "path kernel: scheduler watchdog tripped (%llu warp(s)); the image is incomplete",
@@ -1447,14 +1745,10 @@ int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const
         st->pool_iterations = tot[rtc::ST_POOL_ITERS];
         st->upload_ms = up_ms;
         st->kernel_ms = k_ms;
-        float gms = 0;
-        CU(cudaSetDevice(base));
-        CU(cudaEventElapsedTime(&gms, s0.ev[2], s0.ev[3]));
-        st->gather_ms = gms;
-        st->download_ms = 0; // folded into the caller's wall clock; the copy is asynchronous to ev[3]
+        st->gather_ms = gather_ms;
+        st->download_ms = 0; // folded into the caller's wall clock; the copies are asynchronous to the kernels' events
         st->ngpus_used = G;
-        int per_dev = 1 + (p->ntris > 0) + (p->nspheres > 0) + ((!samples && S > 1) ? 1 : 0);
-        st->kernels_launched = per_dev * G + (G > 1 && !direct ? 1 : 0);
+        st->kernels_launched = (int32_t)(g_launches.load() - launches0);
     }
     if (trace)
         fprintf(stderr, "rtc_b200: render_cuda host timeline: enqueued at %.0f us, synchronised at %.0f us, done at %.0f us\n",
@@ -1474,6 +1768,11 @@ extern "C" int render_cuda(const Scene *scene, const Camera *cam, uint8_t *out_r
         return fail(RTC_ERR_ARG, "render_cuda: triangle / sphere arrays inconsistent with their counts");
     if (p->split_mode != RTC_SPLIT_TILES && p->split_mode != RTC_SPLIT_SAMPLES)
         return fail(RTC_ERR_ARG, "render_cuda: unknown split_mode %d", p->split_mode);
+    if (p->ngpus > 1 && p->split_mode == RTC_SPLIT_SAMPLES && (p->nsplit <= 1 || p->nsplit % p->ngpus))
+        // sub-stream seeds x + y*W + g*W*H are this library's own definition (not the reference's one stream per pixel):
+        // the caller has to ask for them, so that the image never silently depends on the GPU count
+        return fail(RTC_ERR_ARG, "render_cuda: the sample split needs nsplit (sub-streams per pixel) set to a multiple of "
+                                 "ngpus = %d; only the tile split reproduces the reference's image", p->ngpus);
     std::lock_guard<std::mutex> lk(g_ctx.mu);
     return render_locked(scene, cam, out_rgb, p);
 }
@@ -1543,6 +1842,7 @@ int rtc_probe_random_direction(int device, const uint32_t *states, int32_t n, fl
     CU(cudaMalloc(&d_o, sizeof(float) * 3 * (size_t)n));
     CU(cudaMemcpy(d_s, states, sizeof(uint32_t) * (size_t)n, cudaMemcpyHostToDevice));
     probe_random_direction_kernel<<<(n + 127) / 128, 128>>>(d_s, n, d_o, d_os);
+    count_launch();
     CU(cudaGetLastError());
     CU(cudaMemcpy(out, d_o, sizeof(float) * 3 * (size_t)n, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(out_states, d_os, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToHost));
@@ -1566,6 +1866,7 @@ int rtc_probe_environment_light(int device, const Scene *sky, const float *dirs,
     CU(cudaMalloc(&d_o, sizeof(float) * 3 * (size_t)n));
     CU(cudaMemcpy(d_d, dirs, sizeof(float) * 3 * (size_t)n, cudaMemcpyHostToDevice));
     probe_environment_light_kernel<<<(n + 127) / 128, 128>>>(d_d, n, make_sky(sky), d_o);
+    count_launch();
     CU(cudaGetLastError());
     CU(cudaMemcpy(out, d_o, sizeof(float) * 3 * (size_t)n, cudaMemcpyDeviceToHost));
     cudaFree(d_d);
@@ -1593,6 +1894,7 @@ int rtc_fp32_peak_probe(int device, int reps, double *tflops, double *ms_best)
     for (int r = 0; r < (reps > 0 ? reps : 5) + 2; ++r) {
         CU(cudaEventRecord(e0));
         ffma_probe_kernel<<<blocks, threads>>>(buf, iters, 1.000001f, 0.5f);
+        count_launch();
         CU(cudaEventRecord(e1));
         CU(cudaEventSynchronize(e1));
         float ms = 0;
@@ -1628,6 +1930,7 @@ int rtc_uninterleave_device(int device, const void *d_parts, void *d_img, int el
         uninterleave_kernel<uint32_t><<<blocks, 256, 0, st>>>(static_cast<const uint32_t *>(d_parts),
                                                               static_cast<uint32_t *>(d_img), row_elems, height,
                                                               nparts, band_h, part_elems);
+    count_launch();
     CU(cudaGetLastError());
     return RTC_OK;
 }

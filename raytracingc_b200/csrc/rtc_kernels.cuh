@@ -276,7 +276,7 @@ __global__ void __launch_bounds__(CTA_THREADS) render_kernel(const RenderArgs a)
             p[2] = L.acc.z;
         }
         if (a.rgb != nullptr && a.nsplit == 1) { // vec3ToColor, raytracing.c:11-15
-            uint8_t *p = a.rgb + pix * 3;
+            uint8_t *p = a.rgb + pixel_offset(a, (int)pix);
             p[0] = (uint8_t)float_to_uint8(L.acc.x);
             p[1] = (uint8_t)float_to_uint8(L.acc.y);
             p[2] = (uint8_t)float_to_uint8(L.acc.z);

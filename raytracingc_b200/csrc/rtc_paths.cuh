@@ -54,6 +54,8 @@ struct PathWork {
     int spec;                   // 1: group mode runs S consecutive samples of a pixel at once (see the kernel)
     const float4 *qrec;         // MODE >= 1: quick records (4 x float4 per triangle), built by quick_records_kernel
     float obound;               // MODE >= 1: the records are valid for ray origins with max |o_i| <= obound
+    unsigned min_tasks;         // the kernel returns at once when the list holds fewer (pixel, sub-stream) tasks: short
+                                // lists are the pool form's (rtc_pool.cuh), the host launches both
     const float2 *rec;          // with a list: {distance, id bits} of each listed pixel's primary hit, found by the
                                 // primary kernel, which also re-sweeps that ray every sample; nullptr: the path
                                 // kernel sweeps primary rays itself
@@ -630,6 +632,8 @@ __global__ void __launch_bounds__(PATH_THREADS, GROUPS ? PATH_GROUP_CTAS : (MODE
 {
     {
         const unsigned np = w.list ? *w.list_count : (unsigned)(a.out_w * a.out_h);
+        if ((unsigned long long)np * (unsigned)w.planes < (unsigned long long)w.min_tasks)
+            return;
         const bool groups = w.coop && (unsigned long long)np * (unsigned)w.planes * 2ull <= (unsigned long long)w.group_lanes;
         if (groups != GROUPS)
             return;
@@ -732,7 +736,7 @@ __global__ void __launch_bounds__(PATH_THREADS, GROUPS ? PATH_GROUP_CTAS : (MODE
                 p[2] = L.acc.z;
             }
             if (a.rgb != nullptr && a.nsplit == 1 && gr == 0) { // vec3ToColor, raytracing.c:11-15
-                uint8_t *p = a.rgb + (size_t)pix * 3;
+                uint8_t *p = a.rgb + pixel_offset(a, pix);
                 p[0] = (uint8_t)float_to_uint8(L.acc.x);
                 p[1] = (uint8_t)float_to_uint8(L.acc.y);
                 p[2] = (uint8_t)float_to_uint8(L.acc.z);

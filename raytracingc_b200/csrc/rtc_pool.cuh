@@ -36,12 +36,12 @@
 namespace rtc {
 
 #ifndef RTC_POOL_NS
-#define RTC_POOL_NS 96
+#define RTC_POOL_NS 64
 #endif
 // Warps per CTA and CTAs per SM of the resident form (A/B knobs); one CTA of POOL_WARPS_LARGE warps per SM when the
 // scene is large or streamed (the tiles' double buffer is then shared by more warps).
 #ifndef RTC_POOL_WARPS_SMALL
-#define RTC_POOL_WARPS_SMALL 8
+#define RTC_POOL_WARPS_SMALL 12
 #endif
 #ifndef RTC_POOL_MINB_SMALL
 #define RTC_POOL_MINB_SMALL 2
@@ -100,6 +100,8 @@ struct PoolWork {
     const float4 *qrec;         // MODE >= 1: quick records
     float obound;
     unsigned long long watchdog; // scheduler iterations per warp after which the kernel gives up
+    unsigned max_tasks;          // the kernel returns at once when the list holds this many (pixel, sub-stream) tasks or
+                                 // more: long lists are the serial form's (rtc_paths.cuh), the host launches both
 };
 
 __host__ __device__ inline size_t pool_smem_bytes(int ntris, bool stream, int mode, int warps)
@@ -218,6 +220,8 @@ template <bool STREAM, int MODE, int WARPS>
 __global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? POOL_MINB_SMALL : 1) render_pool_kernel(const RenderArgs a, const PoolWork w)
 {
     constexpr int POOL_THREADS = 32 * WARPS;
+    if ((unsigned long long)*w.list_count * (unsigned)w.planes >= (unsigned long long)w.max_tasks)
+        return;
     extern __shared__ float4 sGeo[];
     __shared__ uint64_t bars[2];
     const int ntris = a.sc.ntris;
@@ -423,33 +427,42 @@ __global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? POOL_M
         if (nfree == 0)
             return;
         // demand of this lane's context: one slot when nothing is outstanding (the reference's serial stream), and
-        // speculative children at the next unassigned offsets as far as they can still be needed
+        // speculative children at the next unassigned offsets as far as they can still be needed.  A pixel that keeps
+        // skipping offsets (a closed scene: most of its speculation is dropped) is served last, with the slots nobody
+        // else wants -- idle slots cost nothing, and the slowest pixels are what a short work list waits for.
         unsigned j = 0, top = 0;
         int first = 0, extra = 0;
+        bool good = true;
         if (rem != 0u) {
             j = CXU(C_J);
             top = CXU(C_TOP);
             first = top == j ? 1 : 0;
             if (spec) {
-                // offsets below j + rem can still be needed; a pixel that keeps skipping (closed scenes) runs serially
                 const unsigned consumed = CXU(C_TOTAL) - rem, skipped = j - consumed;
-                if (skipped * 2u <= consumed + 4u)
-                    extra = max(0, min((int)(j + rem - top), POOL_RING - (int)(top - j)) - first);
+                good = skipped * 2u <= consumed + 4u;
+                extra = max(0, min((int)(j + rem - top), POOL_RING - (int)(top - j)) - first); // offsets below j + rem can be needed
             }
         }
         const unsigned fm = __ballot_sync(0xffffffffu, first != 0);
         const int n1 = __popc(fm);
-        const int nwant = __popc(__ballot_sync(0xffffffffu, extra > 0));
-        const int left2 = nfree - n1;
-        extra = (left2 > 0 && nwant > 0) ? min(extra, (left2 + nwant - 1) / nwant) : 0;
-        int p2 = extra; // inclusive scan of the extras
+        const int nwant_g = __popc(__ballot_sync(0xffffffffu, extra > 0 && good));
+        const int nwant_b = __popc(__ballot_sync(0xffffffffu, extra > 0 && !good));
+        const int left2 = max(0, nfree - n1);
+        if (good)
+            extra = nwant_g > 0 ? min(extra, (left2 + nwant_g - 1) / nwant_g) : 0;
+        const int tot_g = min(left2, (int)__reduce_add_sync(0xffffffffu, (unsigned)(good ? extra : 0)));
+        const int left3 = left2 - tot_g;
+        if (!good)
+            extra = nwant_b > 0 ? min(extra, (left3 + nwant_b - 1) / nwant_b) : 0;
+        // positions in the free list: the firsts, then the extras of the well-behaved pixels, then the others'
+        unsigned sc = good ? (unsigned)extra : (unsigned)extra << 16; // both inclusive scans at once
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            const int v = __shfl_up_sync(0xffffffffu, p2, o);
+            const unsigned v = __shfl_up_sync(0xffffffffu, sc, o);
             if (lane >= o)
-                p2 += v;
+                sc += v;
         }
-        p2 = n1 + p2 - extra; // this lane's first extra position in the free list, behind the firsts
+        const int p2 = good ? n1 + (int)(sc & 0xffffu) - extra : n1 + tot_g + (int)(sc >> 16) - extra;
         const int p1 = __popc(fm & lt);
         const int ga = (first && p1 < nfree) ? 1 : 0;
         const int gb = max(0, min(extra, nfree - p2));

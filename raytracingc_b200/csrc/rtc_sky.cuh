@@ -34,6 +34,8 @@ struct SkyWork {
     unsigned *btask_count;
     int tile;             // triangles per streamed tile (<= SKY_TILE)
     int stream;           // 1: stream the table per sample; 0: resident (needs ntris <= SKY_TILE)
+    int segs;             // block kernel: the samples of a sub-stream are split over this many CTAs (blockIdx.z = plane *
+                          // segs + segment) when the pixel grid alone does not fill the machine; >= 1
 };
 
 __host__ __device__ inline size_t sky_smem_bytes(int ntris, bool stream)
@@ -249,7 +251,7 @@ __global__ void __launch_bounds__(FAST_THREADS) render_sky_kernel(const RenderAr
             p[2] = acc.z;
         }
         if (a.rgb != nullptr && a.nsplit == 1) {
-            uint8_t *p = a.rgb + pix * 3;
+            uint8_t *p = a.rgb + pixel_offset(a, (int)pix);
             p[0] = (uint8_t)float_to_uint8(acc.x);
             p[1] = (uint8_t)float_to_uint8(acc.y);
             p[2] = (uint8_t)float_to_uint8(acc.z);

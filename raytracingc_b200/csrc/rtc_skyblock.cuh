@@ -64,7 +64,11 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
     // this lane's block
     const int ci0 = (blockIdx.x * 8 + (lane & 7)) * BLK_W;
     const int cj0 = ((blockIdx.y * SKYB_WARPS + warp) * 4 + (lane >> 3)) * BLK_H;
-    const int g = a.split_first + blockIdx.z;
+    // blockIdx.z = plane * segs + segment: segment 0 owns the classification sample and everything that is written;
+    // the other segments re-sweep their share of the remaining samples (counted and cross-checked, never written)
+    const int segs = w.segs > 0 ? w.segs : 1;
+    const int plane = (int)blockIdx.z / segs, seg = (int)blockIdx.z % segs;
+    const int g = a.split_first + plane;
     unsigned valid = 0;
 #pragma unroll
     for (int p = 0; p < 32; ++p)
@@ -87,6 +91,8 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
     const float ehh = 0.5f * (cy_hi - cy_lo) * 1.001f + 1e-6f * (1.0f + fabsf(wcy));
 
     const int s0 = (int)((long long)g * a.spp / a.nsplit), s1 = (int)((long long)(g + 1) * a.spp / a.nsplit);
+    // this segment's samples [sa, sb): segment 0 takes the first share (classification included)
+    const int sa = s0 + (int)((long long)(s1 - s0) * seg / segs), sb = s0 + (int)((long long)(s1 - s0) * (seg + 1) / segs);
     const float wgt = (float)(1.0 / (double)a.spp);
     unsigned hits0 = 0;    // classification: pixels of this block whose primary ray hits
     bool touched0 = false; // classification: some triangle passed this block's bound
@@ -102,7 +108,7 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
         tma_load_1d(sF + (size_t)(k & 1) * SKY_TILE * TAB_F4, tab + (size_t)t * tile * TAB_F4, bytes, &bars[k & 1]);
     };
 
-    for (int s = s0; s < s1; ++s) {
+    for (int s = sa; s < sb; ++s) {
         bool touched = false; // this block's hitbuf entries are initialised for this sample
         unsigned hits = 0;    // pixels of this block whose primary ray hit (this sample)
         if (stream && threadIdx.x == 0) {
@@ -126,8 +132,11 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
             }
             if (valid == 0 || touched0)
                 smask = 0;
-            if (s != s0) {
+            if (s != sa) {
                 badblocks += smask != 0;
+                smask = 0;
+            } else if (seg != 0 && smask != 0) {
+                touched = true; // a block with candidates: every sample after the classification is the block-task kernel's
                 smask = 0;
             }
             unsigned pending = __ballot_sync(0xffffffffu, smask != 0);
@@ -198,9 +207,12 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
                     }
                     if (valid == 0 || touched0)
                         mask = 0; // a block with candidates at the first sample is re-swept by the block-task kernel
-                    if (s != s0) {
+                    if (s != sa) {
                         // same rays, same arithmetic: a block without candidates at the first sample has none now
                         badblocks += mask != 0;
+                        mask = 0;
+                    } else if (seg != 0 && mask != 0) {
+                        touched = true; // (see the sphere stage)
                         mask = 0;
                     }
                     // ---- first sample: expand surviving blocks, the warp takes one block at a time, one lane
@@ -262,12 +274,12 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
             }
         }
         k0 += (uint32_t)ntiles;
-        if (s == s0 || !touched0)
-            nrays += __popc(valid);
+        if ((s == s0 && seg == 0) || !(s == sa ? touched : touched0))
+            nrays += __popc(valid); // (the other samples of a block with candidates are the block-task kernel's)
 
-        if (s == s0) {
+        if (s == sa) {
             // ---- classification: ids are final, hit pixels go to the path kernel's list ----
-            if (g == a.split_first) {
+            if (g == a.split_first && seg == 0) {
                 if (a.ids != nullptr) {
                     for (int b = 0; b < 32; ++b) { // lane-block b of this warp, one lane per pixel
                         const unsigned bvalid = __shfl_sync(0xffffffffu, valid, b);
@@ -313,16 +325,16 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
             // blocks with candidate triangles: their remaining samples are re-swept pixel by pixel by the
             // block-task kernel (dynamic work queue: these are the expensive blocks, a tile full of them would
             // otherwise be one warp's serial work)
-            if (touched && s + 1 < s1 && w.btask != nullptr) {
+            if (seg == 0 && touched && s + 1 < s1 && w.btask != nullptr) {
                 const unsigned pos = atomicAdd(w.btask_count, 1u);
-                w.btask[pos] = make_int4(ci0, cj0, (int)hits, (int)blockIdx.z);
+                w.btask[pos] = make_int4(ci0, cj0, (int)hits, plane);
             }
         }
     }
 
     // ---- sky pixels: spp identical contributions (same ray, no RNG draw), the reference's serial float adds;
     //      one lane per pixel so the serial chains of 32 pixels run side by side ----
-    const unsigned sky = valid & ~hits0;
+    const unsigned sky = seg == 0 ? valid & ~hits0 : 0u;
     for (int b = 0; b < 32; ++b) {
         const unsigned bsky = __shfl_sync(0xffffffffu, sky, b);
         if (bsky == 0)
@@ -340,13 +352,13 @@ __global__ void __launch_bounds__(SKYB_THREADS) render_skyblock_kernel(const Ren
             acc = xadd3(acc, c);
         const size_t pix = (size_t)cj * a.out_w + ci;
         if (a.accum != nullptr) {
-            float *p = a.accum + ((size_t)blockIdx.z * a.out_w * a.out_h + pix) * 3;
+            float *p = a.accum + ((size_t)plane * a.out_w * a.out_h + pix) * 3;
             p[0] = acc.x;
             p[1] = acc.y;
             p[2] = acc.z;
         }
         if (a.rgb != nullptr && a.nsplit == 1) {
-            uint8_t *p = a.rgb + pix * 3;
+            uint8_t *p = a.rgb + pixel_offset(a, (int)pix);
             p[0] = (uint8_t)float_to_uint8(acc.x);
             p[1] = (uint8_t)float_to_uint8(acc.y);
             p[2] = (uint8_t)float_to_uint8(acc.z);

@@ -75,6 +75,21 @@ FULL = {
 }
 LATTICE = 8
 
+# SURVEY 8d's extra datapoint: the close-up camera (-p 0 -2 -6 -t 0 -1 0), where most pixels hit geometry and the path
+# kernel, not the block bounds, decides the frame (--extra; ~1 CPU-hour)
+EXTRA = {
+    "c4close_ultracomplex_3840x2160_64spp_4b": ("ultracomplex", dict(width=3840, height=2160, spp=64, max_bounce=4,
+                                                                     origin=(0.0, -2.0, -6.0), look_at=(0.0, -1.0, 0.0))),
+}
+
+# BASELINE.json config 5 reduced to what a CPU can check: the synthetic 1 M-triangle scene (rtc_synth_scene, seed 0xB200;
+# host code of the library, SURVEY 8d defines it) at 16 spp, 4 bounces, on the pixels x % 240 == 0, y % 240 == 0 of the 4K
+# frame (16 x 9 pixels: every 60th pixel of the 960 x 540 lattice bench.py --workload c5l renders), for the reference's one
+# stream per pixel and for 2, 4, 8 sub-streams (the sample split's own definition) (--c5; ~1 CPU-minute each)
+C5_TRIS, C5_SEED, C5_STEP = 1 << 20, 0xB200, 240
+C5L = {f"c5l_synth1m_lattice240_16spp_4b_nsplit{g}": dict(width=3840, height=2160, spp=16, max_bounce=4, nsplit=g,
+                                                           row_step=C5_STEP, col_step=C5_STEP) for g in (1, 2, 4, 8)}
+
 
 def load_scene(ref: Oracle, name: str) -> np.ndarray:
     if name == "default":
@@ -125,9 +140,25 @@ def render_parallel(scene: str, kw: dict, P: int):
     return rgb, ids, rgb2, ids2, stats
 
 
+def _c5_worker(args):
+    name, kw = args
+    from raytracingc_b200 import api  # host code only: the scene generator (no GPU needed)
+    tris = api.synth_scene(C5_TRIS, C5_SEED)
+    ref, port = Oracle("reference"), Oracle("port")
+    ref.set_triangles(tris)
+    port.set_triangles(tris)
+    job = Job(**kw)
+    rgb, ids, _ = ref.render(job)
+    rgb2, ids2, st = port.render(job)
+    return name, rgb[::C5_STEP, ::C5_STEP].copy(), ids[::C5_STEP, ::C5_STEP].copy(), \
+        bool((rgb == rgb2).all() and (ids == ids2).all()), st
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--full", action="store_true", help="also the full-size BASELINE.json configs (CPU-minutes)")
+    ap.add_argument("--extra", action="store_true", help="only the close-up 4K frame (about a CPU-hour)")
+    ap.add_argument("--c5", action="store_true", help="only the lattice vectors of the synthetic 1 M-triangle scene")
     ap.add_argument("--procs", type=int, default=os.cpu_count())
     a = ap.parse_args()
 
@@ -147,9 +178,22 @@ def main():
     kat["_scenes"] = counts
     kat["_how"] = "tests/golden/make_golden.py from oracle/_ref (reference functions, gcc -O3 -ffp-contract=off)"
 
+    if a.c5:
+        with mp.Pool(min(a.procs, len(C5L))) as pool:
+            for name, rgb, ids, same, st in pool.imap_unordered(_c5_worker, list(C5L.items())):
+                kat[name] = dict(scene=f"synth:{C5_TRIS}:{C5_SEED:#x}", job=C5L[name], image_fnv=fnv1a64_bytes(rgb),
+                                 id_fnv=fnv1a64_words(ids), hit_pixels=int((ids != -1).sum()), rays=int(st["rays"]),
+                                 port_equals_reference=same, lattice_step=C5_STEP)
+                np.savez_compressed(os.path.join(OUT, "lattice", name + ".npz"), step=C5_STEP, rgb=rgb, ids=ids)
+                print(f"{name}: image {kat[name]['image_fnv']} hits {kat[name]['hit_pixels']} rays {kat[name]['rays']} "
+                      f"port==ref {same}", flush=True)
+                json.dump(kat, open(kat_path, "w"), indent=1, sort_keys=True)
+        return
     todo = dict(SMALL)
     if a.full:
         todo.update(FULL)
+    if a.extra:
+        todo = dict(EXTRA)
     for name, (scene, kw) in todo.items():
         t = time.time()
         rgb, ids, rgb2, ids2, st = render_parallel(scene, kw, a.procs)

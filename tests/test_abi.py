@@ -46,7 +46,7 @@ def test_struct_layouts_match_the_reference(rtc):
     assert C.sizeof(api.Scene) == 56 and C.sizeof(api.Camera) == 52
     assert api.TRI_DTYPE.itemsize == 68 and api.SPHERE_DTYPE.itemsize == 36
     assert api.TRI_DTYPE.fields["normal"][1] == 36 and api.TRI_DTYPE.fields["color"][1] == 48
-    assert C.sizeof(api.RtcSubset) == 20 and C.sizeof(api.RtcDeviceJob) == 64
+    assert C.sizeof(api.RtcSubset) == 20 and C.sizeof(api.RtcDeviceJob) == 68
 
 
 def test_version_and_error_strings(rtc):
@@ -99,6 +99,24 @@ def test_argument_checks(rtc):
         with pytest.raises(rtc.RtcError) as e:
             rtc.render(tris, **args)
         assert e.value.code == 1, kw  # RTC_ERR_ARG comes before any device work
+
+
+def test_sample_split_needs_an_explicit_nsplit(rtc):
+    """The sample split's sub-stream seeds are this library's own definition: render_cuda refuses to pick a count
+    from the number of GPUs (the image would silently depend on it).  Checked before any device work."""
+    from raytracingc_b200 import api
+    tris = np.zeros(1, api.TRI_DTYPE)
+    for nsplit in (0, 1, 3):
+        with pytest.raises(rtc.RtcError) as e:
+            rtc.render(tris, 32, 24, 4, 1, ngpus=2, split_mode=api.RTC_SPLIT_SAMPLES, nsplit=nsplit)
+        assert e.value.code == 1 and "nsplit" in str(e.value)
+
+
+def test_fnv_helper_equals_the_oracle_hash(rtc):
+    from oracle.oracle_api import fnv1a64_bytes
+    from raytracingc_b200 import api
+    a = np.random.default_rng(7).integers(0, 256, 10007, dtype=np.uint8)
+    assert api.fnv1a64(a) == fnv1a64_bytes(a)
 
 
 def test_download_bands_argument_checks(rtc):

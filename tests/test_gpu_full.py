@@ -8,6 +8,8 @@ the image hash equals the golden hash when the libm-dependent sky matches to the
 bit, else (4) the pixels of the committed 8x8 golden lattice are within the
 north_star tolerance.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -33,5 +35,15 @@ def test_full_config(name):
     step, want_rgb, want_ids = util.golden_lattice(name)
     assert (ids[::step, ::step] == want_ids).all()
     r = util.assert_image_parity(rgb[::step, ::step], want_rgb, name)
+    assert st["check_failures"] == 0
+    # The whole frame, bit for bit: the hash of all W*H*3 bytes equals the reference run's.  The one term that is not
+    # reproducible to the last bit offline is glibc's powf in the sky (2.5e-4 of its results differ in the last bit,
+    # tests/test_gpu_math.py), and a last-bit difference of a sky value moves an 8-bit pixel with probability ~1e-5:
+    # should that ever flip a pixel, set RTC_ALLOW_SKY_LSB=1 to fall back to the +-1 LSB rule on the lattice above --
+    # the fallback is reported, never silent.
     exact = fnv1a64_bytes(rgb) == e["image_fnv"]
+    if not exact and os.environ.get("RTC_ALLOW_SKY_LSB") == "1":
+        print(name, "IMAGE HASH DIFFERS from the reference run; +-1 LSB lattice rule applied instead:", r)
+    else:
+        assert exact, f"{name}: image hash {fnv1a64_bytes(rgb)} != reference run {e['image_fnv']} (lattice parity {r})"
     print(name, "image hash identical to the reference run:", exact, r, f"kernel {st['kernel_ms']:.2f} ms")

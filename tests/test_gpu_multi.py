@@ -69,3 +69,32 @@ def test_full_size_c2_over_all_gpus(rtc):
         assert fnv1a64_words(ids) == e["id_fnv"] and fnv1a64_bytes(rgb) == e["image_fnv"]
         assert st["rays"] == e["rays"]
         print(f"C2 on {G} GPUs: kernel {st['kernel_ms']:.2f} ms, gather {st['gather_ms']:.2f} ms")
+
+
+@pytest.mark.parametrize("name", ["ultracomplex_160x90_16spp_4b", "suze_odd_101x67_5spp_2b"])
+def test_ranks_write_their_bands_in_place_over_peer_memory(rtc, name):
+    """RtcDeviceJob.rgb_full: every device stores its pixels at their final address of ONE frame in device 0's memory
+    (peer access over NVLink) -- the frame is assembled by the kernels' own stores, no gather, no un-interleave."""
+    import torch
+    from raytracingc_b200 import api, split
+    e = util.kat()[name]
+    job = util.job_of(e)
+    tris = util.scene_tris(e["scene"])
+    want_rgb, _ = util.golden_image(name)
+    kw = util.gpu_kwargs(job)
+    for G in gpu_counts(rtc):
+        image = torch.zeros((job.height, job.width, 3), dtype=torch.uint8, device="cuda:0")
+        scenes = []
+        for g in range(G):
+            api.enable_peer(g, 0)
+            sc = rtc.DeviceScene(tris, device=g)
+            scenes.append(sc)
+            dj = rtc.DeviceJob(job.width, job.height, job.spp, job.max_bounce, triangles_only=job.triangles_only,
+                               subset=split.band_subset(g, G), rgb_full=1)
+            sc.render(dj, kw["scene"], kw["camera"], d_rgb=image.data_ptr())
+        for g in range(G):
+            torch.cuda.synchronize(g)
+        got = image.cpu().numpy()
+        assert (got == want_rgb).all(), f"G={G}: {(got != want_rgb).any(axis=-1).sum()} pixels differ"
+        for sc in scenes:
+            sc.close()

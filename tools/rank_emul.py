@@ -19,8 +19,9 @@ ap.add_argument("--gpus", type=int, default=8)
 ap.add_argument("--rank", type=int, default=0)
 ap.add_argument("--frames", type=int, default=5)
 a = ap.parse_args()
-scene, W, H, spp, bounce, tonly = bench.WORKLOADS[a.workload]
-tris = bench.load_tris(scene)
+wl = bench.WORKLOADS[a.workload]
+W, H, spp, bounce, tonly = wl["W"], wl["H"], wl["spp"], wl["bounce"], wl["tonly"]
+tris = bench.load_tris(wl["scene"], wl.get("synth", 0))
 sc = rtc.DeviceScene(tris, device=0)
 job = rtc.DeviceJob(W, H, spp, bounce, triangles_only=tonly, subset=split.band_subset(a.rank, a.gpus),
                     flags=api.RTC_FLAG_TIME_KERNELS)
@@ -28,7 +29,8 @@ job.to_c()
 dev = torch.device("cuda", 0)
 rgb = torch.zeros((job.out_h, job.out_w, 3), dtype=torch.uint8, device=dev)
 stats = torch.zeros(24, dtype=torch.int64, device=dev)
-cam, sky = rtc.camera_look_at(), rtc.make_scene()
+cam = rtc.camera_look_at(*wl["camera"]) if wl.get("camera") else rtc.camera_look_at()
+sky = rtc.make_scene()
 st = torch.cuda.current_stream()
 for i in range(a.frames):
     stats.zero_()

@@ -13,8 +13,10 @@ ap.add_argument("--workload", default="c4")
 ap.add_argument("--frames", type=int, default=2)
 ap.add_argument("--flags", type=int, default=0)
 a = ap.parse_args()
-scene, W, H, spp, bounce, tonly = bench.WORKLOADS[a.workload]
-tris = bench.load_tris(scene)
+wl = bench.WORKLOADS[a.workload]
+W, H, spp, bounce, tonly = wl["W"], wl["H"], wl["spp"], wl["bounce"], wl["tonly"]
+tris = bench.load_tris(wl["scene"], wl.get("synth", 0))
+cam = rtc.camera_look_at(*wl["camera"]) if wl.get("camera") else rtc.camera_look_at()
 for i in range(a.frames):
-    rgb, _, st = rtc.render(tris, W, H, spp, bounce, triangles_only=tonly, flags=a.flags)
+    rgb, _, st = rtc.render(tris, W, H, spp, bounce, triangles_only=tonly, flags=a.flags, camera=cam)
     print(f"{a.workload} frame {i}: kernel {st['kernel_ms']:.3f} ms, rays {st['rays']}, upload {st['upload_ms']:.3f} ms")
