@@ -600,7 +600,6 @@ def run_ours(a) -> dict:
                                             "scheduler_iterations": int(pool[5])}}
         if prim_ms:
             line["primary_kernels"] = {"ms": prim_ms, "rays": float(st_p[0]), "pairs_covered": float(st_p[1]),
-                                       "pairs_run_exactly": float(st_p[10]) if len(st_p) > 10 else None,
                                        "note": "conservative block bounds decide most (primary ray, triangle) pairs: a rate, not a "
                                                "roofline fraction (rays * triangles / time would exceed the FP32 peak by design)"}
         if "roofline" not in line:

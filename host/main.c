@@ -52,7 +52,9 @@ static void usage(const char *prog, const char *err)
            "   # SCENE SETTINGS\n\t[-gc|--ground-color <R> <G> <B>]\n\t[-sch|--sky-color-horizon <R> <G> <B>]\n"
            "\t[-scz|--sky-color-zenith <R> <G> <B>]\n"
            "   # SUN SETTINGS\n\t[--sun <x> <y> <z> <focus> <intensity>]\n"
-           "   # RENDER SETTINGS (new)\n\t[--spp <samples per pixel>]\n\t[--gpus <n>]\n\t[--split tiles|samples]\n"
+           "   # RENDER SETTINGS (new)\n\t[--spp <samples per pixel>]\n\t[--gpus <n>]\n"
+           "\t[--split tiles|samples]  (tiles: the reference's image on any GPU count;\n"
+           "\t                          samples: needs --nsplit, a multiple of --gpus -- its own RNG sub-streams)\n"
            "\t[--nsplit <sub-streams>]\n\t[--triangles path/to/triangles.txt]\n",
            prog);
     exit(0); /* the reference exits 0 from its usage text, errors included (main.c:63) */
