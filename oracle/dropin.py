@@ -21,6 +21,7 @@ ROOT = os.path.dirname(HERE)
 REF = "/root/reference"
 OUT_DIR = os.path.join(HERE, "_ref", "dropin")
 BINARY = os.path.join(OUT_DIR, "rayt_dropin")
+STOCK = os.path.join(OUT_DIR, "rayt_stock")  # the UNMODIFIED reference program (12 pthreads), timed for the record
 
 # what replaces main.c:285-302
 CALL = r'''
@@ -96,6 +97,10 @@ def build(verbose: bool = False) -> str:
     with tempfile.TemporaryDirectory(prefix="rtc_dropin_") as tmp:
         src = os.path.join(tmp, "ref")
         shutil.copytree(REF, src, ignore=shutil.ignore_patterns(".git", "*.o", "*.out", "*.bmp"))
+        # the stock program first, from the untouched copy (the reference's own Makefile puts -lm before the objects and
+        # fails to link on this toolchain, SURVEY fact 9: same sources, same -O3, libraries at the end)
+        subprocess.run(["gcc", "-O3", "-w", "main.c", "raytracing.c", "moremath.c", "objloader.c", "-o", STOCK, "-lm", "-lpthread"],
+                       cwd=src, check=True)
         patch_sources(src)
         cmd = ["gcc", "-O3", "-w", "-I" + os.path.join(ROOT, "include"), "main.c", "raytracing.c", "moremath.c", "objloader.c",
                "-o", BINARY, "-L" + lib_dir, "-lrtc_b200", "-Wl,-rpath,$ORIGIN/../../../raytracingc_b200", "-lm", "-lpthread"]

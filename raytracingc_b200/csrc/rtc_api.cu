@@ -1510,6 +1510,7 @@ int device_finish(const Call &c, int g, DevResult &r)
 //      synchronisations run side by side instead of one after the other on the caller's thread ----
 class DeviceWorkers {
   public:
+    ~DeviceWorkers() { stop(); } // a process that never called render_cuda_shutdown() still joins its threads at exit
     void run(int n, const std::function<void(int)> &fn) // fn(1) .. fn(n - 1) on workers, fn(0) on the caller; waits for all
     {
         {

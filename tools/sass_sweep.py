@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """Extract the branch-free first phase of the path kernel's sweep (the hot loop) from the built library's SASS.
 
-usage: python tools/sass_sweep.py [MODE] > profiles/rNN_sass_sweep.txt   (MODE 3 = packed quick records, 1 = scalar quick records, 0 = reference arithmetic)
+usage: python tools/sass_sweep.py [MODE] [serial|pool] > profiles/rNN_sass_sweep.txt
+       (MODE 3 = packed quick records, 1 = scalar quick records, 0 = reference arithmetic; pool = render_pool_kernel, two rays per lane)
 The loop is found as the call-free, convergence-barrier-free backward branch whose body has the most FP32 arithmetic."""
 import os
 import re
@@ -10,10 +11,11 @@ import sys
 from collections import Counter
 
 mode = sys.argv[1] if len(sys.argv) > 1 else "3"
+form = sys.argv[2] if len(sys.argv) > 2 else "serial"
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 lib = os.path.join(root, "raytracingc_b200", "librtc_b200.so")
 txt = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True, check=True).stdout
-name = f"_ZN3rtc19render_paths_kernelILb0ELi{mode}E"
+name = f"_ZN3rtc19render_paths_kernelILb0ELi{mode}E" if form == "serial" else f"_ZN3rtc18render_pool_kernelILb0ELi{mode}ELi12E"
 lines, on = [], False
 for l in txt.splitlines():
     if "Function :" in l:
@@ -37,9 +39,14 @@ for l in body:
     t = re.sub(r"/\*[0-9a-f]+\*/", "", l).split()
     ops[(t[1] if t[0].startswith("@") else t[0]).split(".")[0]] += 1
 per = max(1, ops["LDS"] // (3 if mode == "0" else 4))  # 4 LDS.128 of quick record per triangle (3 of geometry in mode 0)
-print(f"render_paths_kernel<false, {mode}> (sm_100a, cuobjdump -sass of raytracingc_b200/librtc_b200.so): the branch-free")
-print(f"first phase of sweep_chunked (rtc_paths.cuh), {per} triangles per iteration: {len(body)} instructions = "
-      f"{len(body) / per:.2f} per (ray, triangle) pair.")
+if form == "pool":
+    print(f"render_pool_kernel<false, {mode}, 12> (sm_100a, cuobjdump -sass of raytracingc_b200/librtc_b200.so): the branch-free")
+    print(f"first phase of sweep_two (rtc_pool.cuh), {per} triangles x TWO rays per iteration (every LDS.128 feeds both rays): "
+          f"{len(body)} instructions = {len(body) / (2 * per):.2f} per (ray, triangle) pair.")
+else:
+    print(f"render_paths_kernel<false, {mode}> (sm_100a, cuobjdump -sass of raytracingc_b200/librtc_b200.so): the branch-free")
+    print(f"first phase of sweep_chunked (rtc_paths.cuh), {per} triangles per iteration: {len(body)} instructions = "
+          f"{len(body) / per:.2f} per (ray, triangle) pair.")
 if mode in ("3", "4"):
     print("Two triangles per packed instruction (FFMA2 / FMUL2 / FADD2 on pair-interleaved records, the ray's scalars as the")
     print("broadcast operand Rx.F32); per-pair data by warp-uniform LDS.128; survivors set one bit of the lane's mask through")
