@@ -1213,12 +1213,13 @@ struct DeviceSlot {
     float *accum = nullptr; // tile split with nsplit > 1: local sub-stream planes
     size_t accum_bytes = 0;
     // single-GPU frames: the image goes to the host in row chunks, each as soon as its pixels are final
-    cudaStream_t copy = nullptr;
+    cudaStream_t copy[4] = {nullptr, nullptr, nullptr, nullptr}; // chunk k goes out on copy[k % COPY_STREAMS]
     unsigned *prog = nullptr; // 3 * COPY_CHUNKS words, see RenderArgs::prog
     unsigned long long *h_stats = nullptr; // page-locked: the counters arrive with the frame, no extra blocking copy
 };
 
 constexpr int COPY_CHUNKS = 16;
+constexpr int COPY_STREAMS = 4; // a chunk that waits for its last pixel only holds back every fourth chunk behind it
 using WaitValue32Fn = int (*)(cudaStream_t, unsigned long long, unsigned, unsigned); // cuStreamWaitValue32
 WaitValue32Fn wait_value32()
 {
@@ -1290,6 +1291,35 @@ __global__ void uninterleave_kernel(const T *__restrict__ all, T *__restrict__ i
     img[i] = all[(size_t)g * part_elems + (size_t)j * W_elems + xe];
 }
 
+// Bands [band_lo, band_hi) of one part of a band split (the part's compact rows, band after band) to their rows of a HOST
+// image: one strided device->host copy (+ one for a cut last band).
+int download_band_range(int device, const void *d_part, void *h_img, size_t row_bytes, int height, int nparts, int band_h,
+                        int part, int band_lo, int band_hi, cudaStream_t st)
+{
+    CU(cudaSetDevice(device));
+    const size_t band_bytes = (size_t)band_h * row_bytes, stride = (size_t)nparts * band_bytes;
+    // bands of this part: rows [b * nparts * band_h + part * band_h, + band_h) for b = 0, 1, ... while inside the image
+    const int first = part * band_h, period = nparts * band_h;
+    if (first >= height)
+        return RTC_OK;
+    const int nb = (height - first + period - 1) / period;                        // bands that start inside the image
+    const int last_rows = std::min(band_h, height - (first + (nb - 1) * period)); // rows of the last one
+    const int nfull = last_rows == band_h ? nb : nb - 1;
+    const int lo = std::max(0, band_lo), hi = std::min(nb, band_hi);
+    if (lo >= hi)
+        return RTC_OK;
+    char *dst = static_cast<char *>(h_img) + (size_t)first * row_bytes;
+    const char *src = static_cast<const char *>(d_part);
+    const int full_hi = std::min(hi, nfull);
+    if (full_hi > lo)
+        CU(cudaMemcpy2DAsync(dst + (size_t)lo * stride, stride, src + (size_t)lo * band_bytes, band_bytes, band_bytes,
+                             (size_t)(full_hi - lo), cudaMemcpyDeviceToHost, st));
+    if (hi > nfull && nfull >= lo) // the cut last band
+        CU(cudaMemcpyAsync(dst + (size_t)nfull * stride, src + (size_t)nfull * band_bytes, (size_t)last_rows * row_bytes,
+                           cudaMemcpyDeviceToHost, st));
+    return RTC_OK;
+}
+
 } // namespace
 
 namespace {
@@ -1321,8 +1351,9 @@ extern "C" void render_cuda_shutdown(void)
         cudaFree(s.accum);
         cudaFree(s.prog);
         cudaFreeHost(s.h_stats);
-        if (s.copy)
-            cudaStreamDestroy(s.copy);
+        for (auto &cs : s.copy)
+            if (cs)
+                cudaStreamDestroy(cs);
         s = DeviceSlot();
     }
 }
@@ -1376,6 +1407,9 @@ struct DevResult {
     bool touched = false; // asynchronous work of this call may be in flight on the device's streams
 };
 
+int download_band_range(int device, const void *d_part, void *h_img, size_t row_bytes, int height, int nparts, int band_h,
+                        int part, int band_lo, int band_hi, cudaStream_t st);
+
 // Everything device g does for the frame, queued asynchronously: upload + flatten, render, and -- unless a collective
 // follows (NCCL modes) -- the copy of its pixels into the caller's image.
 int device_enqueue(const Call &c, int g, DevResult &r)
@@ -1403,8 +1437,9 @@ int device_enqueue(const Call &c, int g, DevResult &r)
             return rc;
     r.touched = true;
     if (c.pipelined) {
-        if (!s.copy)
-            CU(cudaStreamCreateWithFlags(&s.copy, cudaStreamNonBlocking));
+        for (auto &cs : s.copy)
+            if (!cs)
+                CU(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
         if (!s.prog)
             CU(cudaMalloc(&s.prog, sizeof(unsigned) * 3 * COPY_CHUNKS));
         if (!s.scene->sky_ev)
@@ -1436,28 +1471,37 @@ int device_enqueue(const Call &c, int g, DevResult &r)
     CU(cudaEventRecord(s.ev[2], s.stream));
     // the counters travel with the frame (page-locked buffer): no blocking copy after the synchronisation
     CU(cudaMemcpyAsync(s.h_stats, s.stats, sizeof(unsigned long long) * RTC_DEVICE_STATS_WORDS, cudaMemcpyDeviceToHost, s.stream));
-    if (c.direct) {
+    if (c.pipelined) {
+        // The copy streams follow the kernels: sky pixels are final after the classification kernel, the rows of a chunk
+        // once the path kernel has finished its last primary-hit pixel (flag set on the device; rtc_render_device sets
+        // every flag at the end of the frame whatever path it took).  Chunks go out round-robin on COPY_STREAMS streams so
+        // that the sky-only chunks behind the geometry do not queue up behind the chunk that finishes last.
+        const uint8_t *d_final = static_cast<const uint8_t *>(s.part);
+        const int part_rows = c.job[g].out_h;
+        for (auto &cs : s.copy)
+            CU(cudaStreamWaitEvent(cs, s.scene->sky_ev, 0));
+        for (int k = 0; k < COPY_CHUNKS; ++k) {
+            const int r0 = k * c.chunk_rows;
+            if (r0 >= part_rows)
+                break;
+            const int r1 = std::min(part_rows, r0 + c.chunk_rows);
+            cudaStream_t cs = s.copy[k % COPY_STREAMS];
+            if (wait_value32()(cs, (unsigned long long)(uintptr_t)(s.prog + 2 * COPY_CHUNKS + k), 1u, 0u /* GEQ */) != 0)
+                return fail(RTC_ERR_CUDA, "cuStreamWaitValue32 failed");
+            if (c.direct) { // this device's bands r0/8 .. of its compact part, to their rows of the caller's image
+                if ((rc = download_band_range(dev, s.part, c.out_rgb, (size_t)c.W * 3, c.H, c.G, BAND_H, g, r0 / BAND_H,
+                                              (r1 + BAND_H - 1) / BAND_H, cs)))
+                    return rc;
+            } else {
+                CU(cudaMemcpyAsync(c.out_rgb + (size_t)r0 * c.W * 3, d_final + (size_t)r0 * c.W * 3, (size_t)(r1 - r0) * c.W * 3,
+                                   cudaMemcpyDeviceToHost, cs));
+            }
+        }
+    } else if (c.direct) {
         if ((rc = rtc_download_bands(dev, s.part, c.out_rgb, (size_t)c.W * 3, c.H, c.G, BAND_H, g, s.stream)))
             return rc;
     } else if (c.G == 1) {
-        const uint8_t *d_final = static_cast<const uint8_t *>(s.part);
-        if (c.pipelined) {
-            // the copy stream follows the kernels: sky pixels are final after the classification kernel, the rows of
-            // a chunk once the path kernel has finished its last primary-hit pixel (flag set on the device;
-            // rtc_render_device sets every flag at the end of the frame whatever path it took)
-            CU(cudaStreamWaitEvent(s.copy, s.scene->sky_ev, 0));
-            for (int k = 0; k < COPY_CHUNKS; ++k) {
-                const size_t r0 = (size_t)k * c.chunk_rows;
-                if (r0 >= (size_t)c.H)
-                    break;
-                const size_t r1 = std::min<size_t>((size_t)c.H, r0 + c.chunk_rows);
-                if (wait_value32()(s.copy, (unsigned long long)(uintptr_t)(s.prog + 2 * COPY_CHUNKS + k), 1u, 0u /* GEQ */) != 0)
-                    return fail(RTC_ERR_CUDA, "cuStreamWaitValue32 failed");
-                CU(cudaMemcpyAsync(c.out_rgb + r0 * c.W * 3, d_final + r0 * c.W * 3, (r1 - r0) * c.W * 3, cudaMemcpyDeviceToHost, s.copy));
-            }
-        } else {
-            CU(cudaMemcpyAsync(c.out_rgb, d_final, c.img_bytes, cudaMemcpyDeviceToHost, s.stream));
-        }
+        CU(cudaMemcpyAsync(c.out_rgb, s.part, c.img_bytes, cudaMemcpyDeviceToHost, s.stream));
     }
     return RTC_OK;
 }
@@ -1470,8 +1514,9 @@ void device_drain(const Call &c, int g)
     cudaSetDevice(c.base + g);
     if (s.stream)
         cudaStreamSynchronize(s.stream);
-    if (s.copy)
-        cudaStreamSynchronize(s.copy);
+    for (auto &cs : s.copy)
+        if (cs)
+            cudaStreamSynchronize(cs);
     if (s.scene)
         s.scene->prog = nullptr;
     cudaGetLastError();
@@ -1486,7 +1531,8 @@ int device_finish(const Call &c, int g, DevResult &r)
     CU(cudaSetDevice(dev));
     CU(cudaStreamSynchronize(s.stream));
     if (c.pipelined)
-        CU(cudaStreamSynchronize(s.copy));
+        for (auto &cs : s.copy)
+            CU(cudaStreamSynchronize(cs));
     memcpy(r.h, s.h_stats, sizeof r.h);
     CU(cudaEventElapsedTime(&r.up_ms, s.ev[0], s.ev[1]));
     CU(cudaEventElapsedTime(&r.k_ms, s.ev[1], s.ev[2]));
@@ -1647,9 +1693,12 @@ int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const
     c.part_bytes = c.samples ? (size_t)(c.S / G) * c.img_bytes * sizeof(float) : (size_t)c.job[0].out_h * W * 3; // device 0 owns the most rows
     // one GPU, plain frame: the device->host copy runs chunk by chunk on its own stream, behind the kernels
     // (only frames whose copy takes long enough to be worth 2 x COPY_CHUNKS more runtime calls)
-    c.pipelined = G == 1 && c.S == 1 && H >= 8 * COPY_CHUNKS && c.img_bytes >= (size_t)env_int("RTC_PIPELINE_MIN_BYTES", 4 << 20) &&
-                  wait_value32() != nullptr && getenv("RTC_NO_PIPELINE") == nullptr;
-    c.chunk_rows = ((H + COPY_CHUNKS - 1) / COPY_CHUNKS + 7) / 8 * 8; // whole 8 x 4 pixel blocks
+    // (G > 1, tile split: the same per device, over the rows of its compact part)
+    const int part_rows = c.job[0].out_h;
+    c.pipelined = (G == 1 || c.direct) && c.S == 1 && part_rows >= 8 * COPY_CHUNKS &&
+                  c.part_bytes >= (size_t)env_int("RTC_PIPELINE_MIN_BYTES", 4 << 20) && wait_value32() != nullptr &&
+                  getenv("RTC_NO_PIPELINE") == nullptr;
+    c.chunk_rows = ((part_rows + COPY_CHUNKS - 1) / COPY_CHUNKS + 7) / 8 * 8; // whole 8 x 4 pixel blocks and whole bands
 
     DevResult res[MAX_GPUS];
     int rc = RTC_OK;
@@ -1945,24 +1994,8 @@ int rtc_download_bands(int device, const void *d_part, void *h_img, size_t row_b
 {
     if (!d_part || !h_img || row_bytes == 0 || height <= 0 || nparts <= 0 || band_h <= 0 || part < 0 || part >= nparts)
         return fail(RTC_ERR_ARG, "download_bands: bad arguments");
-    CU(cudaSetDevice(device));
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const size_t band_bytes = (size_t)band_h * row_bytes, stride = (size_t)nparts * band_bytes;
-    // bands of this part: rows [b * nparts * band_h + part * band_h, + band_h) for b = 0, 1, ... while inside the image
-    const int first = part * band_h, period = nparts * band_h;
-    if (first >= height)
-        return RTC_OK;
-    const int nb = (height - first + period - 1) / period;                        // bands that start inside the image
-    const int last_rows = std::min(band_h, height - (first + (nb - 1) * period)); // rows of the last one
-    const int nfull = last_rows == band_h ? nb : nb - 1;
-    char *dst = static_cast<char *>(h_img) + (size_t)first * row_bytes;
-    const char *src = static_cast<const char *>(d_part);
-    if (nfull > 0)
-        CU(cudaMemcpy2DAsync(dst, stride, src, band_bytes, band_bytes, (size_t)nfull, cudaMemcpyDeviceToHost, st));
-    if (nfull < nb)
-        CU(cudaMemcpyAsync(dst + (size_t)nfull * stride, src + (size_t)nfull * band_bytes, (size_t)last_rows * row_bytes,
-                           cudaMemcpyDeviceToHost, st));
-    return RTC_OK;
+    return download_band_range(device, d_part, h_img, row_bytes, height, nparts, band_h, part, 0, 1 << 30,
+                               static_cast<cudaStream_t>(stream));
 }
 
 } // extern "C"

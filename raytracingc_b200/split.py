@@ -53,3 +53,12 @@ def substreams_of(rank: int, world: int, nsplit: int) -> tuple:
         raise ValueError(f"nsplit ({nsplit}) must be a multiple of the rank count ({world})")
     per = nsplit // world
     return rank * per, per
+
+
+def image_row(rank: int, world: int, j: int, band_h: int = BAND_H) -> int:
+    """Image row of compact row `j` of `rank`'s part: where a rank that writes IN PLACE (RtcDeviceJob.rgb_full, the
+    frame assembled by the kernels' own stores into one buffer) puts it -- the host mirror of pixel_offset() in
+    csrc/rtc_scene.cuh: y = row_start + (j // band_h) * row_step + j % band_h."""
+    if world <= 1:
+        return j
+    return rank * band_h + (j // band_h) * world * band_h + j % band_h

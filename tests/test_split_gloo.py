@@ -73,6 +73,61 @@ def test_band_split_all_gather(world, name, port_oracle):
     assert nrows > 0
 
 
+def _worker_in_place(rank, world, port, name, shm_path, q):
+    """every rank writes its rows straight into ONE frame (here: a file in /dev/shm mapped by all ranks) at their final
+    addresses -- the host mirror of the peer-write assembly (RtcDeviceJob.rgb_full): no gather, no un-interleave"""
+    import torch
+    import torch.distributed as dist
+    from oracle.oracle_api import Oracle
+    from raytracingc_b200 import split
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    e = util.kat()[name]
+    job = util.job_of(e)
+    W, H = job.width, job.height
+    o = Oracle("port")
+    o.set_triangles(util.scene_tris(e["scene"]))
+    frame = np.memmap(shm_path, dtype=np.uint8, mode="r+", shape=(H, W, 3))
+    rows = split.rows_of(rank, world, H)
+    scratch = np.zeros((H, W, 3), np.uint8)
+    for j in range(len(rows)):
+        y = split.image_row(rank, world, j)
+        assert y == rows[j]
+        job.row_start, job.row_step = y, H
+        o.render(job, want_ids=False, out=(scratch, None))
+        frame[y] = scratch[y]  # the rank's own store, at the row's final address
+    frame.flush()
+    dist.barrier()
+    if rank == 0:
+        want, _ = util.golden_image(name)
+        q.put(bool((np.asarray(frame) == want).all()))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,name", [(2, "suze_odd_101x67_5spp_2b"), (4, "default_64x64_16spp_4b")])
+def test_band_split_written_in_place(world, name, port_oracle, tmp_path):
+    import torch.multiprocessing as mp
+    e = util.kat()[name]
+    job = util.job_of(e)
+    shm = f"/dev/shm/rtc_b200_test_{os.getpid()}_{world}"
+    with open(shm, "wb") as f:
+        f.truncate(job.width * job.height * 3)
+    try:
+        ctx = mp.get_context("spawn")
+        q = ctx.Queue()
+        port = _free_port()
+        procs = [ctx.Process(target=_worker_in_place, args=(r, world, port, name, shm, q)) for r in range(world)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(180)
+            assert p.exitcode == 0
+        assert q.get(timeout=5) is True
+    finally:
+        os.unlink(shm)
+
+
 def test_split_bookkeeping():
     from raytracingc_b200 import split
     for world in (1, 2, 3, 4, 8):
