@@ -687,7 +687,13 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
                              (force && strcmp(force, "serial") == 0);
     const bool want_pool = force && strcmp(force, "pool") == 0;
     unsigned split_at = 0; // lists shorter than this go to the pool form
-    if (pool_ok && !want_serial) {
+    // a streamed scene (tiles of a large scene through shared memory, CTA-synchronous sweeps) stays with the serial form
+    // unless the pool is asked for: a sweep then costs a pass over the whole scene, and the serial form's cooperative
+    // sweep of few rays (S lanes per ray) is the better answer to a sparse second bounce (measured on the 1 M-triangle
+    // lattice: 2.9e11 against 1.3e11 pairs/s)
+    const bool streamed = env_int("RTC_FORCE_STREAM", 0) != 0 ||
+                          rtc::pool_smem_bytes(sc->ntris, false, mode, rtc::POOL_WARPS_LARGE) > (size_t)sc->max_smem_optin;
+    if (pool_ok && !want_serial && (!streamed || want_pool)) {
         const unsigned serial_lanes = (unsigned)sc->nsm * 6u * rtc::PATH_THREADS;
         split_at = want_pool ? 0xffffffffu : (unsigned)((unsigned long long)serial_lanes * (unsigned)std::max(0, env_int("RTC_POOL_MAX_FACTOR", 125)) / 100u);
         int rc_p = launch_pool(sc, a, list, rec, planes, mode, split_at, st);
