@@ -251,6 +251,32 @@ int rtc_uninterleave_device(int device, const void *d_parts, void *d_img, int el
 int rtc_download_bands(int device, const void *d_part, void *h_img, size_t row_bytes, int height, int nparts, int band_h,
                        int part, void *stream);
 
+/*
+ * NO COUNTERPART IN THE REFERENCE -- added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * The path kernel (rtc::render_paths_kernel: every ray of every sample of every pixel against every triangle, the
+ * brute-force form that RTC_FLAG_PATHS_ONLY selects in rtc_render_device) with ALL of its scratch -- the work cursor
+ * and the per-scene quick records of the sweep's conservative first phase -- in ONE file-scope
+ * `static __device__ __align__(256)` array of the library instead of buffers of the scene handle.  The call
+ * allocates nothing: no cudaMalloc, no cudaFree, no allocating library routine.  Inputs and outputs are the
+ * caller's: an existing scene handle (its flattened triangle buffers were allocated by rtc_scene_create, outside
+ * the no-allocation region), sky, camera, job, and the device buffers d_rgb (required), d_ids, d_stats (optional),
+ * with the meaning they have in rtc_render_device.  The image is bit-identical to rtc_render_device's.
+ *
+ * Limits: at most RTC_NOALLOC_MAX_TRIS triangles in the scene (more -> RTC_ERR_ARG, nothing is launched); the
+ * reference's one RNG stream per pixel only (job->nsplit <= 1); job->maxBounce >= 1.  The array is
+ * RTC_NOALLOC_SCRATCH_BYTES (about 144 KB) and every GPU that loads the library holds it until the process exits.
+ * EVERY call on a device shares that one array and finds the previous call's contents in it: each call clears the
+ * cursor words and rebuilds the quick records for its scene on `stream` before its kernel -- so calls are correct
+ * back to back on one stream (or otherwise ordered on the GPU), and two calls that OVERLAP on the same GPU
+ * (different streams, no dependency) RACE on the array.
+ */
+#define RTC_NOALLOC_MAX_TRIS 2048
+#define RTC_NOALLOC_SCRATCH_BYTES 147856 /* 256 + 144 per pair of triangles, RTC_NOALLOC_MAX_TRIS / 2 + 1 pairs (checked in rtc_api.cu) */
+int rtc_render_paths_noalloc(const RtcScene *scene, const Scene *sky, const Camera *cam, const RtcDeviceJob *job,
+                             uint8_t *d_rgb, int32_t *d_ids, uint64_t *d_stats, void *stream);
+
 /* Dependent-free FFMA probe: measured FP32 peak of `device` in TFLOP/s (2 flop per FFMA), best of `reps`.
  * The roofline denominator of the intersection kernel (MEASURED_PEAKS.json has no FP32 figure). */
 int rtc_fp32_peak_probe(int device, int reps, double *tflops, double *ms_best);

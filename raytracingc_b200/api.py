@@ -30,6 +30,7 @@ RTC_SPLIT_TILES, RTC_SPLIT_SAMPLES = 0, 1
 RTC_FLAG_COUNT_EXITS, RTC_FLAG_EXACT_ONLY, RTC_FLAG_PATHS_ONLY, RTC_FLAG_PER_PAIR_FILTER, RTC_FLAG_TIME_KERNELS = 1, 2, 4, 8, 16
 RTC_FLAG_VERIFY_QUICK, RTC_FLAG_REF_QUICK, RTC_FLAG_SERIAL_PATHS = 32, 64, 128
 STATS_WORDS = 24
+RTC_NOALLOC_MAX_TRIS = 2048  # include/rtc_b200.h
 ERRORS = {1: "RTC_ERR_ARG", 2: "RTC_ERR_NO_GPU", 3: "RTC_ERR_CUDA", 4: "RTC_ERR_NCCL", 5: "RTC_ERR_NOMEM"}
 
 # the sphere the reference hard-codes (scene.h:17-19); used when trianglesOnly == 0
@@ -95,7 +96,7 @@ EXPORTS = ["render_cuda", "render_cuda_shutdown", "rtc_camera_look_at", "rtc_nor
            "rtc_render_device", "rtc_sum_quantize_device", "rtc_quantize_device", "rtc_render_launch_count",
            "rtc_uninterleave_device", "rtc_download_bands", "rtc_fp32_peak_probe", "rtc_scene_update", "rtc_scene_kernel_times", "rtc_synth_scene",
            "rtc_probe_random_direction", "rtc_probe_environment_light", "rtc_launches_total", "rtc_ipc_export",
-           "rtc_ipc_open", "rtc_ipc_close", "rtc_enable_peer", "rtc_fnv1a64"]
+           "rtc_ipc_open", "rtc_ipc_close", "rtc_enable_peer", "rtc_fnv1a64", "rtc_render_paths_noalloc"]
 
 
 def load_library() -> C.CDLL:
@@ -171,6 +172,9 @@ def load_library() -> C.CDLL:
     lib.rtc_enable_peer.restype = C.c_int
     lib.rtc_fnv1a64.argtypes = [C.c_void_p, C.c_size_t]
     lib.rtc_fnv1a64.restype = C.c_uint64
+    lib.rtc_render_paths_noalloc.argtypes = [C.c_void_p, P(Scene), P(Camera), P(RtcDeviceJob), C.c_void_p, C.c_void_p,
+                                             C.c_void_p, C.c_void_p]
+    lib.rtc_render_paths_noalloc.restype = C.c_int
     _lib = lib
     return lib
 
@@ -306,6 +310,16 @@ class DeviceScene:
         _check(load_library().rtc_render_device(self.handle, C.byref(scene), C.byref(camera), C.byref(j),
                                                 d_rgb or None, d_accum or None, d_ids or None, d_stats or None,
                                                 stream or None))
+        return j
+
+    def render_noalloc(self, job: DeviceJob, scene: Scene, camera: Camera, d_rgb: int, d_ids: int = 0, d_stats: int = 0,
+                       stream: int = 0) -> RtcDeviceJob:
+        """rtc_render_paths_noalloc: the path kernel with its scratch in the library's static device array -- no
+        allocation inside the call (no counterpart in the reference).  <= RTC_NOALLOC_MAX_TRIS
+        triangles; calls that overlap on one GPU race on the shared array."""
+        j = job.to_c()
+        _check(load_library().rtc_render_paths_noalloc(self.handle, C.byref(scene), C.byref(camera), C.byref(j), d_rgb or None,
+                                                       d_ids or None, d_stats or None, stream or None))
         return j
 
     def update(self, tris: np.ndarray, spheres: np.ndarray | None = None, stream: int = 0):

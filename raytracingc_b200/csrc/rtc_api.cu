@@ -2005,3 +2005,126 @@ int rtc_download_bands(int device, const void *d_part, void *h_img, size_t row_b
 }
 
 } // extern "C"
+
+// ---- rtc_render_paths_noalloc: the path kernel with its scratch in a static device array ---------------------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Declaration and contract:
+// include/rtc_b200.h.  This block only ADDS an entry point: it launches the existing kernels
+// (quick_records_kernel, render_paths_kernel) with pointers into the array below instead of the scene handle's
+// cudaMalloc'ed scratch, and changes no other code path.
+
+namespace {
+
+constexpr size_t NOALLOC_HEAD_BYTES = 256; // work cursor + counters of the path kernel; cleared by every call
+constexpr size_t NOALLOC_QREC_F4 = (size_t)rtc::QPAIR_F4 * (RTC_NOALLOC_MAX_TRIS / 2 + 1); // pair records, packed layout
+static_assert(NOALLOC_HEAD_BYTES + NOALLOC_QREC_F4 * sizeof(float4) == RTC_NOALLOC_SCRATCH_BYTES,
+              "RTC_NOALLOC_SCRATCH_BYTES of rtc_b200.h is out of date");
+
+// [cursor words (256 B)][quick records of up to RTC_NOALLOC_MAX_TRIS triangles].  One per GPU that loads the library,
+// held until exit, shared by every call: it keeps the LAST call's contents.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[RTC_NOALLOC_SCRATCH_BYTES];
+
+// In host code `g_noalloc_scratch` is a host-side stand-in for the symbol, NOT a device address: the address a kernel
+// may be given comes from cudaGetSymbolAddress, asked once per device with that device current.
+int noalloc_scratch_address(int device, unsigned char **out)
+{
+    static unsigned char *addr[MAX_GPUS] = {nullptr};
+    static std::mutex mu;
+    if (device < 0 || device >= MAX_GPUS)
+        return fail(RTC_ERR_ARG, "render_paths_noalloc: device %d out of range", device);
+    std::lock_guard<std::mutex> lk(mu);
+    if (!addr[device]) {
+        CU(cudaSetDevice(device));
+        void *p = nullptr;
+        CU(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        if (!p)
+            return fail(RTC_ERR_CUDA, "render_paths_noalloc: cudaGetSymbolAddress returned a null address");
+        addr[device] = static_cast<unsigned char *>(p);
+    }
+    *out = addr[device];
+    return RTC_OK;
+}
+
+} // namespace
+
+extern "C" int rtc_render_paths_noalloc(const RtcScene *sc, const Scene *sky, const Camera *cam, const RtcDeviceJob *job,
+                                        uint8_t *d_rgb, int32_t *d_ids, uint64_t *d_stats, void *stream)
+{
+    int rc = check_job(sc, sky, cam, job);
+    if (rc)
+        return rc;
+    if (!d_rgb)
+        return fail(RTC_ERR_ARG, "render_paths_noalloc: d_rgb is required");
+    if (sc->ntris > RTC_NOALLOC_MAX_TRIS)
+        return fail(RTC_ERR_ARG, "render_paths_noalloc: the scene has %d triangles, the static scratch holds the records of at "
+                                 "most RTC_NOALLOC_MAX_TRIS = %d (use rtc_render_device)", sc->ntris, RTC_NOALLOC_MAX_TRIS);
+    if (job->nsplit > 1)
+        return fail(RTC_ERR_ARG, "render_paths_noalloc: nsplit = %d; only the reference's one RNG stream per pixel", job->nsplit);
+    if (job->maxBounce < 1)
+        return fail(RTC_ERR_ARG, "render_paths_noalloc: needs maxBounce >= 1");
+    if (job->out_w == 0 || job->out_h == 0)
+        return RTC_OK;
+    CU(cudaSetDevice(sc->device));
+    unsigned char *scratch = nullptr;
+    if ((rc = noalloc_scratch_address(sc->device, &scratch)))
+        return rc;
+    cudaGetLastError(); // a stale error of an earlier, unrelated call must not be blamed on the launches below
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+
+    rtc::RenderArgs a = make_args(sc, sky, cam, job);
+    a.rgb = d_rgb;
+    a.ids = d_ids;
+    a.stats = reinterpret_cast<unsigned long long *>(d_stats);
+
+    // what must start at zero: the work cursor (the array keeps the previous call's value)
+    CU(cudaMemsetAsync(scratch, 0, NOALLOC_HEAD_BYTES, st));
+    // quick records: packed form when the stored normals follow the winding (as rtc_render_device decides), else the
+    // reference-arithmetic first phase, which needs no records.  Rebuilt by EVERY call: the array is shared by all
+    // scenes and calls, whatever it holds belongs to the last one.
+    const int mode = sc->quick_ok ? 3 : 0;
+    rtc::PathWork w;
+    memset(&w, 0, sizeof w);
+    if (mode != 0) {
+        float need = std::fmax(sc->bound_abs, std::fmax(std::fabs(a.origin.x), std::fmax(std::fabs(a.origin.y), std::fabs(a.origin.z))));
+        need = (need * 1.001f + 1e-6f) * 1.25f; // the primary rays start at the camera: it counts for the origin bound
+        float4 *qrec = reinterpret_cast<float4 *>(scratch + NOALLOC_HEAD_BYTES);
+        if (sc->ntris > 0) {
+            rtc::quick_records_kernel<<<(sc->ntris + 127) / 128, 128, 0, st>>>(sc->geo, sc->ntris, need, qrec, rtc::mode_layout(mode));
+            count_launch();
+            CU(cudaGetLastError());
+        }
+        w.qrec = qrec;
+        w.obound = need;
+    }
+    w.list = nullptr; // every pixel of the subset; the kernel sweeps the primary rays itself
+    w.rec = nullptr;
+    w.list_count = reinterpret_cast<unsigned *>(scratch);
+    w.cursor = reinterpret_cast<unsigned *>(scratch) + 1;
+    w.planes = 1;
+    w.write_ids = 1;
+    w.tile = rtc::PATH_TILE;
+    w.coop = 1;
+    w.group_lanes = 0; // the plain (GROUPS = false) instantiation
+    w.spec = 0;
+    w.spec_fails = 2;
+    w.spec_retry = 0;
+    w.min_tasks = 0;
+    const bool streamed = rtc::path_smem_bytes(sc->ntris, false, mode) > 96 * 1024; // tiles through shared memory (TMA)
+    const size_t smem = rtc::path_smem_bytes(sc->ntris, streamed, mode);
+    using PathKernel = void (*)(const rtc::RenderArgs, const rtc::PathWork);
+    const PathKernel kern = mode == 3 ? (streamed ? rtc::render_paths_kernel<true, 3, false> : rtc::render_paths_kernel<false, 3, false>)
+                                      : (streamed ? rtc::render_paths_kernel<true, 0, false> : rtc::render_paths_kernel<false, 0, false>);
+    int per_sm = 0, nsm = 0;
+    if ((rc = kernel_occupancy(sc->device, reinterpret_cast<const void *>(kern), rtc::PATH_THREADS, smem, &per_sm))) // no allocation
+        return rc;
+    if (per_sm < 1)
+        return fail(RTC_ERR_CUDA, "render_paths_noalloc: path kernel does not fit on an SM (smem %zu)", smem);
+    CU(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, sc->device));
+    const long long tasks = (long long)a.out_w * a.out_h;
+    const long long want = (tasks + rtc::PATH_THREADS - 1) / rtc::PATH_THREADS;
+    const int blocks = (int)std::min<long long>((long long)nsm * per_sm, want > 0 ? want : 1);
+    kern<<<blocks, rtc::PATH_THREADS, smem, st>>>(a, w);
+    count_launch();
+    CU(cudaGetLastError());
+    return RTC_OK;
+}
