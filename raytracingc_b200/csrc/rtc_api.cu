@@ -115,6 +115,10 @@ struct RtcScene {
     // pipelined device->host copy of render_cuda (one-shot, consumed by the next render): see RenderArgs::prog
     unsigned *prog = nullptr;
     int prog_rows = 0, prog_chunks = 0;
+    // length of the last frame's work list, copied to a page-locked word behind the block-task kernel (off the critical
+    // path).  Only a HINT for which form of the path kernel to queue first (both stay correct whatever it says).
+    unsigned *h_list_len = nullptr;
+    bool list_len_seen = false;
     cudaEvent_t sky_ev = nullptr; // recorded when every pixel no later kernel rewrites is final (sky pixels)
     bool sky_recorded = false;
 };
@@ -236,6 +240,7 @@ void rtc_scene_destroy(RtcScene *sc)
     cudaFree(sc->sphq);
     cudaFree(sc->qrec);
     cudaFree(sc->counters);
+    cudaFreeHost(sc->h_list_len);
     for (auto &e : sc->kev)
         if (e)
             cudaEventDestroy(e);
@@ -481,6 +486,8 @@ bool camera_is_orthonormal(const Camera *c)
 // cudaFuncSetAttribute + occupancy query of a kernel at a dynamic shared-memory size.  Both runtime calls cost
 // several microseconds and a frame makes a dozen of them, so the opt-in limit is only ever raised (it is sticky per
 // function) and the occupancy is remembered per (device, kernel, size).
+int env_int(const char *name, int dflt);
+
 int kernel_occupancy(int device, const void *kern, int threads, size_t smem, int *per_sm)
 {
     using FnKey = std::pair<int, const void *>;
@@ -492,6 +499,9 @@ int kernel_occupancy(int device, const void *kern, int threads, size_t smem, int
     auto li = limit.find(fk);
     if (li == limit.end() || li->second < smem) {
         CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if (env_int("RTC_CARVEOUT", 0) != 0) // A/B knob: every render kernel asks for the largest shared-memory carve-out, so that
+                                             // kernels of different footprints can follow each other without reconfiguring the SMs
+            CU(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
         limit[fk] = smem;
     }
     auto oi = occupancy.find({fk, smem});
@@ -544,6 +554,10 @@ int ensure_scratch(RtcScene *sc, size_t npix, size_t nbtask = 0)
     }
     if (!sc->counters)
         CU(cudaMalloc(&sc->counters, 8 * sizeof(unsigned)));
+    if (!sc->h_list_len) {
+        CU(cudaMallocHost(&sc->h_list_len, sizeof(unsigned)));
+        *sc->h_list_len = 0u;
+    }
     if (npix > sc->cap_list || !sc->list) {
         CU(cudaFree(sc->list));
         sc->list = nullptr;
@@ -687,6 +701,7 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
                              (force && strcmp(force, "serial") == 0);
     const bool want_pool = force && strcmp(force, "pool") == 0;
     unsigned split_at = 0; // lists shorter than this go to the pool form
+    bool pool_deferred = false, pool_only = false;
     // a streamed scene (tiles of a large scene through shared memory, CTA-synchronous sweeps) stays with the serial form
     // unless the pool is asked for: a sweep then costs a pass over the whole scene, and the serial form's cooperative
     // sweep of few rays (S lanes per ray) is the better answer to a sparse second bounce (measured on the 1 M-triangle
@@ -696,9 +711,22 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
     if (pool_ok && !want_serial && (!streamed || want_pool)) {
         const unsigned serial_lanes = (unsigned)sc->nsm * 6u * rtc::PATH_THREADS;
         split_at = want_pool ? 0xffffffffu : (unsigned)((unsigned long long)serial_lanes * (unsigned)std::max(0, env_int("RTC_POOL_MAX_FACTOR", 125)) / 100u);
-        int rc_p = launch_pool(sc, a, list, rec, planes, mode, split_at, st);
-        if (rc_p || want_pool)
-            return rc_p;
+        // Which of the two is queued first matters (C4, one B200: an empty pool launch in front of the serial form costs
+        // 0.07 ms -- its large shared-memory footprint breaks the overlap with the block-task kernel --, an empty serial
+        // launch in front of the pool form 0.11 ms on a 1/8 share): the form that is EXPECTED to run goes first.  With
+        // fewer pixels than the threshold the list is certainly short and the serial form is not launched at all;
+        // otherwise the previous frame's list length decides (a hint, read without synchronisation; the first frame
+        // queues the pool form first).  RTC_POOL_LAST=0|1 forces the order.
+        const long long max_tasks = (long long)a.out_w * a.out_h * planes;
+        pool_only = !want_pool && max_tasks < (long long)split_at;
+        const bool hint_long = sc->list_len_seen && planes == 1 && sc->h_list_len != nullptr &&
+                               *(volatile unsigned *)sc->h_list_len >= split_at;
+        pool_deferred = !want_pool && !pool_only && env_int("RTC_POOL_LAST", hint_long ? 1 : 0) != 0;
+        if (!pool_deferred) {
+            int rc_p = launch_pool(sc, a, list, rec, planes, mode, split_at, st);
+            if (rc_p || want_pool || pool_only)
+                return rc_p;
+        }
     }
     w.qrec = nullptr;
     w.obound = 0.f;
@@ -764,6 +792,8 @@ int launch_paths(RtcScene *sc, const rtc::RenderArgs &a, const int *list, const 
         count_launch();
     }
     CU(cudaGetLastError());
+    if (pool_deferred)
+        return launch_pool(sc, a, list, rec, planes, mode, split_at, st);
     return RTC_OK;
 }
 
@@ -1058,6 +1088,10 @@ static int render_device_impl(const RtcScene *sc, const Scene *sky, const Camera
                 rtc::render_blocktask_kernel<<<msc->nsm * per_sm, rtc::BTASK_THREADS, tsmem, ts>>>(a, msc->tab, tw);
                 count_launch();
                 CU(cudaGetLastError());
+                if (planes == 1 && env_int("RTC_NO_HINT", 0) == 0) { // this frame's list length, for the next frame's launch order (see launch_paths)
+                    CU(cudaMemcpyAsync(msc->h_list_len, msc->counters, sizeof(unsigned), cudaMemcpyDeviceToHost, ts));
+                    msc->list_len_seen = true;
+                }
                 if (overlap)
                     CU(cudaEventRecord(msc->join_ev, msc->aux));
                 rc = launch_paths(msc, a, msc->list, msc->rec, planes, 0, job->flags, st);
@@ -1220,11 +1254,12 @@ struct DeviceSlot {
     size_t accum_bytes = 0;
     // single-GPU frames: the image goes to the host in row chunks, each as soon as its pixels are final
     cudaStream_t copy[4] = {nullptr, nullptr, nullptr, nullptr}; // chunk k goes out on copy[k % COPY_STREAMS]
-    unsigned *prog = nullptr; // 3 * COPY_CHUNKS words, see RenderArgs::prog
+    unsigned *prog = nullptr; // 3 * MAX_COPY_CHUNKS words, see RenderArgs::prog
     unsigned long long *h_stats = nullptr; // page-locked: the counters arrive with the frame, no extra blocking copy
 };
 
-constexpr int COPY_CHUNKS = 16;
+constexpr int COPY_CHUNKS = 16;     // row chunks of a pipelined frame (RTC_COPY_CHUNKS, A/B knob)
+constexpr int MAX_COPY_CHUNKS = 64;
 constexpr int COPY_STREAMS = 4; // a chunk that waits for its last pixel only holds back every fourth chunk behind it
 using WaitValue32Fn = int (*)(cudaStream_t, unsigned long long, unsigned, unsigned); // cuStreamWaitValue32
 WaitValue32Fn wait_value32()
@@ -1401,7 +1436,7 @@ struct Call {
     bool direct;    // tile split, G > 1: every device copies its own bands into the caller's image
     bool pipelined; // G == 1: row chunks go to the host as soon as their pixels are final
     size_t img_bytes, part_bytes;
-    int chunk_rows;
+    int chunk_rows, nchunks;
     RtcDeviceJob job[MAX_GPUS];
 };
 
@@ -1447,13 +1482,13 @@ int device_enqueue(const Call &c, int g, DevResult &r)
             if (!cs)
                 CU(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
         if (!s.prog)
-            CU(cudaMalloc(&s.prog, sizeof(unsigned) * 3 * COPY_CHUNKS));
+            CU(cudaMalloc(&s.prog, sizeof(unsigned) * 3 * MAX_COPY_CHUNKS));
         if (!s.scene->sky_ev)
             CU(cudaEventCreateWithFlags(&s.scene->sky_ev, cudaEventDisableTiming));
-        CU(cudaMemsetAsync(s.prog, 0, sizeof(unsigned) * 3 * COPY_CHUNKS, s.stream));
+        CU(cudaMemsetAsync(s.prog, 0, sizeof(unsigned) * 3 * MAX_COPY_CHUNKS, s.stream));
         s.scene->prog = s.prog;
         s.scene->prog_rows = c.chunk_rows;
-        s.scene->prog_chunks = COPY_CHUNKS;
+        s.scene->prog_chunks = c.nchunks;
     }
     CU(cudaEventRecord(s.ev[0], s.stream));
     CU(cudaMemsetAsync(s.stats, 0, sizeof(unsigned long long) * RTC_DEVICE_STATS_WORDS, s.stream));
@@ -1486,13 +1521,13 @@ int device_enqueue(const Call &c, int g, DevResult &r)
         const int part_rows = c.job[g].out_h;
         for (auto &cs : s.copy)
             CU(cudaStreamWaitEvent(cs, s.scene->sky_ev, 0));
-        for (int k = 0; k < COPY_CHUNKS; ++k) {
+        for (int k = 0; k < c.nchunks; ++k) {
             const int r0 = k * c.chunk_rows;
             if (r0 >= part_rows)
                 break;
             const int r1 = std::min(part_rows, r0 + c.chunk_rows);
             cudaStream_t cs = s.copy[k % COPY_STREAMS];
-            if (wait_value32()(cs, (unsigned long long)(uintptr_t)(s.prog + 2 * COPY_CHUNKS + k), 1u, 0u /* GEQ */) != 0)
+            if (wait_value32()(cs, (unsigned long long)(uintptr_t)(s.prog + 2 * c.nchunks + k), 1u, 0u /* GEQ */) != 0)
                 return fail(RTC_ERR_CUDA, "cuStreamWaitValue32 failed");
             if (c.direct) { // this device's bands r0/8 .. of its compact part, to their rows of the caller's image
                 if ((rc = download_band_range(dev, s.part, c.out_rgb, (size_t)c.W * 3, c.H, c.G, BAND_H, g, r0 / BAND_H,
@@ -1701,10 +1736,11 @@ int render_locked(const Scene *scene, const Camera *cam, uint8_t *out_rgb, const
     // (only frames whose copy takes long enough to be worth 2 x COPY_CHUNKS more runtime calls)
     // (G > 1, tile split: the same per device, over the rows of its compact part)
     const int part_rows = c.job[0].out_h;
-    c.pipelined = (G == 1 || c.direct) && c.S == 1 && part_rows >= 8 * COPY_CHUNKS &&
+    c.nchunks = std::max(1, std::min(env_int("RTC_COPY_CHUNKS", COPY_CHUNKS), MAX_COPY_CHUNKS));
+    c.pipelined = (G == 1 || c.direct) && c.S == 1 && part_rows >= 8 * c.nchunks &&
                   c.part_bytes >= (size_t)env_int("RTC_PIPELINE_MIN_BYTES", 4 << 20) && wait_value32() != nullptr &&
                   getenv("RTC_NO_PIPELINE") == nullptr;
-    c.chunk_rows = ((part_rows + COPY_CHUNKS - 1) / COPY_CHUNKS + 7) / 8 * 8; // whole 8 x 4 pixel blocks and whole bands
+    c.chunk_rows = ((part_rows + c.nchunks - 1) / c.nchunks + 7) / 8 * 8; // whole 8 x 4 pixel blocks and whole bands
 
     DevResult res[MAX_GPUS];
     int rc = RTC_OK;

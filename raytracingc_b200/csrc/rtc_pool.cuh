@@ -46,12 +46,16 @@ namespace rtc {
 #ifndef RTC_POOL_MINB_SMALL
 #define RTC_POOL_MINB_SMALL 2
 #endif
+#ifndef RTC_POOL_DONE_BATCH // finished samples a warp lets accumulate before it runs consume + refill while its passes are full
+#define RTC_POOL_DONE_BATCH 16
+#endif
 #ifndef RTC_POOL_UP // pair records per iteration of the two-ray quick test
 #define RTC_POOL_UP 1
 #endif
 constexpr int POOL_WARPS_SMALL = RTC_POOL_WARPS_SMALL, POOL_WARPS_LARGE = 16, POOL_MINB_SMALL = RTC_POOL_MINB_SMALL;
 constexpr int POOL_NS = RTC_POOL_NS; // evaluation slots per warp (multiple of 32)
 constexpr int POOL_NC = 32;          // pixel contexts per warp: context c belongs to lane c
+constexpr int POOL_DONE_BATCH = RTC_POOL_DONE_BATCH;
 constexpr int POOL_SPL = (POOL_NS + 31) / 32; // slots a lane looks after (lane, lane + 32, ...; the last row may be cut)
 #ifndef RTC_POOL_RING
 #define RTC_POOL_RING 32
@@ -279,6 +283,7 @@ __global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? POOL_M
                                               ((unsigned long long)nwarps * w.ctx_share_div)));
     const float fh = (float)(a.H / 2);
     const float wgt = (float)(1.0 / (double)a.spp); // main.c:99
+    const float inv2w = 0.5f / (float)nwarps;
 
     bool exhausted = total == 0;
     unsigned seen = 0; // the list position after this warp's last fetch
@@ -378,7 +383,7 @@ __global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? POOL_M
             const int nlive = 32 - __popc(idle);
             // guided: towards the end of the list the warps take fewer pixels at a time
             const unsigned left = total - min(seen, total);
-            const unsigned guide = max(1u, left / (2u * nwarps));
+            const unsigned guide = max(1u, (unsigned)((float)left * inv2w)); // ~ left / (2 warps), no integer division
             const int nnew = min(max(0, min(__popc(idle), maxctx - nlive)), (int)min(guide, 32u));
             if (nnew > 0) {
                 unsigned base = 0;
@@ -390,8 +395,8 @@ __global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? POOL_M
                     exhausted = true;
                 const unsigned t = base + (unsigned)__popc(idle & lt);
                 if (rem == 0u && __popc(idle & lt) < nnew && t < total) {
-                    const int plane = (int)(t / npix);
-                    const unsigned li = t % npix;
+                    const int plane = w.planes == 1 ? 0 : (int)(t / npix);
+                    const unsigned li = w.planes == 1 ? t : t % npix;
                     const int pix = w.list[li];
                     const float2 hit = w.rec[li];
                     const int ci = pix % a.out_w, cj = pix / a.out_w;
@@ -400,7 +405,11 @@ __global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? POOL_M
                     const int g = a.split_first + plane;
                     const float dx = xdiv((float)(x - a.W / 2), fh), dy = xdiv((float)(y - a.H / 2), fh); // main.c:88-94
                     const f3 pdir = xnormalize(xadd3(xadd3(xscale3(a.ex, dx), xscale3(a.ey, dy)), xscale3(a.ez, a.fov)));
-                    const int s_begin = (int)((long long)g * a.spp / a.nsplit), s_end = (int)((long long)(g + 1) * a.spp / a.nsplit);
+                    int s_begin = 0, s_end = a.spp;
+                    if (a.nsplit != 1) { // (64-bit divisions: only for sub-streams)
+                        s_begin = (int)((long long)g * a.spp / a.nsplit);
+                        s_end = (int)((long long)(g + 1) * a.spp / a.nsplit);
+                    }
                     rem = (unsigned)(s_end - s_begin);
                     CXU(C_PIX) = (unsigned)pix;
                     CXU(C_PLANE) = (unsigned)plane;
@@ -448,12 +457,13 @@ __global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? POOL_M
         const int nwant_g = __popc(__ballot_sync(0xffffffffu, extra > 0 && good));
         const int nwant_b = __popc(__ballot_sync(0xffffffffu, extra > 0 && !good));
         const int left2 = max(0, nfree - n1);
+        // (quotas by a float quotient rounded up: any value is safe, the positions below are clipped to the free list)
         if (good)
-            extra = nwant_g > 0 ? min(extra, (left2 + nwant_g - 1) / nwant_g) : 0;
+            extra = nwant_g > 0 ? min(extra, __float2int_ru(__fdividef((float)left2, (float)nwant_g))) : 0;
         const int tot_g = min(left2, (int)__reduce_add_sync(0xffffffffu, (unsigned)(good ? extra : 0)));
         const int left3 = left2 - tot_g;
         if (!good)
-            extra = nwant_b > 0 ? min(extra, (left3 + nwant_b - 1) / nwant_b) : 0;
+            extra = nwant_b > 0 ? min(extra, __float2int_ru(__fdividef((float)left3, (float)nwant_b))) : 0;
         // positions in the free list: the firsts, then the extras of the well-behaved pixels, then the others'
         unsigned sc = good ? (unsigned)extra : (unsigned)extra << 16; // both inclusive scans at once
 #pragma unroll
@@ -650,19 +660,31 @@ __global__ void __launch_bounds__(32 * WARPS, WARPS == POOL_WARPS_SMALL ? POOL_M
                 tripped = true;
                 break;
             }
-            __syncwarp();
-            consume();
-            __syncwarp();
-            refill();
-            __syncwarp();
-            int nshade = 0, nsweep = 0;
+            // census of the slots; consume + refill (a few hundred instructions) only when enough samples have finished to
+            // be worth it, or when the runnable work would not fill a pass -- they hand out work, they do not create it
+            int nshade = 0, nsweep = 0, ndone = 0, nfree = 0;
+            auto census = [&]() {
+                nshade = nsweep = ndone = nfree = 0;
 #pragma unroll
-            for (int k = 0; k < POOL_SPL; ++k) {
-                const unsigned st = lane + 32 * k < POOL_NS ? SLU(E_META, lane + 32 * k) & 3u : (unsigned)SL_FREE;
-                sb[k] = __ballot_sync(0xffffffffu, st == SL_SHADE);
-                wb[k] = __ballot_sync(0xffffffffu, st == SL_SWEEP);
-                nshade += __popc(sb[k]);
-                nsweep += __popc(wb[k]);
+                for (int k = 0; k < POOL_SPL; ++k) {
+                    const bool in = lane + 32 * k < POOL_NS;
+                    const unsigned st = in ? SLU(E_META, lane + 32 * k) & 3u : (unsigned)SL_FREE;
+                    sb[k] = __ballot_sync(0xffffffffu, st == SL_SHADE);
+                    wb[k] = __ballot_sync(0xffffffffu, st == SL_SWEEP);
+                    nshade += __popc(sb[k]);
+                    nsweep += __popc(wb[k]);
+                    ndone += __popc(__ballot_sync(0xffffffffu, st == SL_DONE));
+                    nfree += __popc(__ballot_sync(0xffffffffu, in && st == SL_FREE));
+                }
+            };
+            __syncwarp();
+            census();
+            if ((ndone >= POOL_DONE_BATCH || (nsweep < 64 && nshade < 32)) && (ndone > 0 || nfree > 0)) {
+                consume();
+                __syncwarp();
+                refill();
+                __syncwarp();
+                census();
             }
             // the pass that fills its lanes better; a streamed sweep costs a pass over the whole scene: fill it
             const int esw = STREAM ? (nsweep >= 64 || nshade == 0 ? 64 : 0) : min(64, nsweep);
