@@ -46,7 +46,7 @@ def collect_r2p(src):
             line = last_json(os.path.join(src, f))
             if line:
                 open(os.path.join(dst, "r2_" + f), "w").write(line + "\n")
-    for f in ("launches_bench_c4.csv", "c5_lattice.txt", "pytest_gpu.log", "pipe_probe.txt", "sweep_probe.txt", "stock_rayt_c1.txt"):
+    for f in ("launches_bench_c4.csv", "c5_lattice.txt", "pytest_gpu.log", "pipe_probe.txt", "sweep_probe.txt", "stock_rayt_c1.txt", "e2e_trace_c4.txt"):
         if os.path.exists(os.path.join(src, f)) and os.path.getsize(os.path.join(src, f)) > 0:
             shutil.copy(os.path.join(src, f), os.path.join(dst, "r2_" + f))
     if os.path.exists(os.path.join(src, "fp32_peak.json")):

@@ -42,7 +42,8 @@ print(json.dumps({"fp32_ffma_tflops": vals, "best": max(vals), "nominal": 2 * 12
 PY
 # the stock 12-thread reference binary on C1 at its compiled-in 4000 spp, for the record
 if [ -x oracle/_ref/dropin/rayt_stock ]; then
-  ( cd oracle/_ref/dropin && nproc && /usr/bin/time -v ./rayt_stock -i 3Dmodels/simplest.obj -s 320 240 -b 1 -o /tmp/stock_c1.bmp ) > $O/stock_rayt_c1.txt 2>&1; grep -E "Elapsed|Maximum resident|^[0-9]+$" $O/stock_rayt_c1.txt | head
+  ( cd oracle/_ref/dropin && echo "host cores: $(nproc); the UNMODIFIED reference program (12 pthreads, 4000 spp compiled in), C1 = simplest.obj 320x240, 1 bounce:" && TIMEFORMAT='wall %R s, user %U s, sys %S s' && time ./rayt_stock -i 3Dmodels/simplest.obj -s 320 240 -b 1 -o /tmp/stock_c1.bmp > /dev/null ) > $O/stock_rayt_c1.txt 2>&1; cat $O/stock_rayt_c1.txt
 fi
 python tools/c5_lattice.py --step 8 --spp 2 --flags 16 > $O/c5_lattice.txt 2>&1
+RTC_TRACE=1 python tools/e2e_trace.py --frames 10 > $O/e2e_trace_c4.txt 2> $O/e2e_trace_c4.err; grep timeline $O/e2e_trace_c4.err | tail -n 3 >> $O/e2e_trace_c4.txt
 ls -la $O | head -60
