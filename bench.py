@@ -336,19 +336,37 @@ def run_ours(a) -> dict:
         # rank 0 owns the frame; the others open it over CUDA IPC and write their pixels at their final addresses
         handle = [api.ipc_export(local, image.data_ptr()) if rank == 0 else None]
         dist.broadcast_object_list(handle, src=0)
-        if rank == 0:
-            d_rgb = image.data_ptr()
+        ok = 1
+        try:
+            if rank != 0:
+                if os.environ.get("RTC_BENCH_FORCE_IPC_FAIL"):
+                    raise rtc.RtcError(3, "forced by RTC_BENCH_FORCE_IPC_FAIL")
+                peer_ptr = api.ipc_open(local, handle[0])
+        except rtc.RtcError as exc:  # no peer access between these devices: every rank falls back to the gather
+            ok = 0
+            print(f"bench.py: rank {rank} cannot map rank 0's frame ({exc}); falling back to --gather nccl", file=sys.stderr)
+        t_ok = torch.tensor([ok], device=dev)
+        dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
+        if int(t_ok[0]) == 1:
+            d_rgb = image.data_ptr() if rank == 0 else peer_ptr
         else:
-            peer_ptr = api.ipc_open(local, handle[0])
-            d_rgb = peer_ptr
-    elif G > 1:  # --gather nccl: compact parts, all_gather, un-interleave on rank 0
+            if peer_ptr:
+                api.ipc_close(local, peer_ptr)
+                peer_ptr = 0
+            peer = False
+            a.gather = "nccl"
+            job.rgb_full = 0
+            job.to_c()
+            if image is None:
+                image = torch.zeros((full_h, full_w, 3), dtype=torch.uint8, device=dev)
+    if G > 1 and not samples and not peer:  # --gather nccl: compact parts, all_gather, un-interleave on rank 0
         job0 = rtc.DeviceJob(W, H, spp, bounce, triangles_only=tonly, subset=(0, G * BAND_H, 0, 1, BAND_H))
         job0.to_c()
         part_h = job0.out_h  # rank 0 owns the most rows; parts are padded to it for the all_gather
         part = torch.zeros((part_h, W, 3), dtype=torch.uint8, device=dev)
         gathered = torch.zeros((G, part_h, W, 3), dtype=torch.uint8, device=dev)
         d_rgb = part.data_ptr()
-    else:
+    if G == 1:
         d_rgb = image.data_ptr()
     host_img = torch.empty((full_h, full_w, 3), dtype=torch.uint8).pin_memory()
     host_tris = torch.from_numpy(tris.view(np.uint8).copy()).pin_memory()
