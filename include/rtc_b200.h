@@ -286,6 +286,11 @@ int rtc_fp32_peak_probe(int device, int reps, double *tflops, double *ms_best);
  * each) on n independent inputs, so that the FP64 islands can be compared with the reference at scale. */
 int rtc_probe_random_direction(int device, const uint32_t *states, int32_t n, float *out, uint32_t *out_states);
 int rtc_probe_environment_light(int device, const Scene *sky, const float *dirs, int32_t n, float *out);
+/* Self-check of the normal deviate (RandomValueNormalDistrubtion, moremath.c:98-103): the device evaluates it by short
+ * tailored approximations + a Ziv check and falls back to the reference's sequence when the check cannot decide.  For the
+ * `count` generator states from `first_state` on (2^32 = every state the reference can reach) this compares the two, bit
+ * for bit: out[0] = decided and different (must be 0), out[1] = declined (fell back), out[2] = states checked. */
+int rtc_probe_normal_selfcheck(int device, uint32_t first_state, uint64_t count, uint64_t out[3]);
 
 #ifdef __cplusplus
 }

@@ -96,7 +96,7 @@ EXPORTS = ["render_cuda", "render_cuda_shutdown", "rtc_camera_look_at", "rtc_nor
            "rtc_render_device", "rtc_sum_quantize_device", "rtc_quantize_device", "rtc_render_launch_count",
            "rtc_uninterleave_device", "rtc_download_bands", "rtc_fp32_peak_probe", "rtc_scene_update", "rtc_scene_kernel_times", "rtc_synth_scene",
            "rtc_probe_random_direction", "rtc_probe_environment_light", "rtc_launches_total", "rtc_ipc_export",
-           "rtc_ipc_open", "rtc_ipc_close", "rtc_enable_peer", "rtc_fnv1a64", "rtc_render_paths_noalloc"]
+           "rtc_ipc_open", "rtc_ipc_close", "rtc_enable_peer", "rtc_fnv1a64", "rtc_render_paths_noalloc", "rtc_probe_normal_selfcheck"]
 
 
 def load_library() -> C.CDLL:
@@ -175,6 +175,8 @@ def load_library() -> C.CDLL:
     lib.rtc_render_paths_noalloc.argtypes = [C.c_void_p, P(Scene), P(Camera), P(RtcDeviceJob), C.c_void_p, C.c_void_p,
                                              C.c_void_p, C.c_void_p]
     lib.rtc_render_paths_noalloc.restype = C.c_int
+    lib.rtc_probe_normal_selfcheck.argtypes = [C.c_int, C.c_uint32, C.c_uint64, P(C.c_uint64)]
+    lib.rtc_probe_normal_selfcheck.restype = C.c_int
     _lib = lib
     return lib
 
@@ -426,6 +428,13 @@ def probe_random_direction(states: np.ndarray, device: int = 0):
     after = np.empty(len(st), dtype=np.uint32)
     _check(load_library().rtc_probe_random_direction(device, st.ctypes.data, len(st), out.ctypes.data, after.ctypes.data))
     return out, after
+
+
+def probe_normal_selfcheck(first_state: int = 0, count: int = 1 << 32, device: int = 0) -> dict:
+    """Fast path of the normal deviate against the exact sequence on `count` generator states (default: all 2^32)."""
+    out = (C.c_uint64 * 3)()
+    _check(load_library().rtc_probe_normal_selfcheck(device, first_state & 0xFFFFFFFF, count, out))
+    return {"different": int(out[0]), "declined": int(out[1]), "states": int(out[2])}
 
 
 def probe_environment_light(dirs: np.ndarray, scene: Scene | None = None, device: int = 0) -> np.ndarray:

@@ -1918,6 +1918,63 @@ __global__ void probe_environment_light_kernel(const float *dirs, int n, rtc::Sk
 }
 } // namespace
 
+// Exhaustive self-check of the normal deviate's fast path (rtc_math.cuh): for the `count` generator states from `first`
+// on, the two draws a deviate consumes, then the fast path against the exact sequence, bit for bit.
+// out[0] = states where the fast path decided AND differs (must be 0), out[1] = states it declined (fall back), out[2] = states.
+namespace {
+__global__ void probe_normal_selfcheck_kernel(uint32_t first, unsigned long long count, unsigned long long *out)
+{
+    unsigned long long bad = 0, declined = 0, n = 0;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < count;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        uint32_t st = first + (uint32_t)i;
+        const float u1 = rtc::random_value(st), u2 = rtc::random_value(st);
+        float v;
+        const bool ok = rtc::nf::normal_fast(u1, u2, v);
+        const float ref = rtc::normal_from_draws_exact(u1, u2);
+        if (!ok)
+            declined++;
+        else if (__float_as_uint(v) != __float_as_uint(ref))
+            bad++;
+        n++;
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        bad += __shfl_xor_sync(0xffffffffu, bad, o);
+        declined += __shfl_xor_sync(0xffffffffu, declined, o);
+        n += __shfl_xor_sync(0xffffffffu, n, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&out[0], bad);
+        atomicAdd(&out[1], declined);
+        atomicAdd(&out[2], n);
+    }
+}
+} // namespace
+
+int rtc_probe_normal_selfcheck(int device, uint32_t first_state, uint64_t count, uint64_t out[3])
+{
+    if (!out)
+        return fail(RTC_ERR_ARG, "probe_normal_selfcheck: NULL");
+    if (rtc_device_count() <= device || device < 0)
+        return fail(RTC_ERR_NO_GPU, "probe_normal_selfcheck: device %d not visible", device);
+    CU(cudaSetDevice(device));
+    unsigned long long *d = nullptr;
+    CU(cudaMalloc(&d, 3 * sizeof(unsigned long long)));
+    CU(cudaMemset(d, 0, 3 * sizeof(unsigned long long)));
+    int nsm = 0;
+    CU(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, device));
+    probe_normal_selfcheck_kernel<<<nsm * 8, 256>>>(first_state, (unsigned long long)count, d);
+    count_launch();
+    CU(cudaGetLastError());
+    unsigned long long h[3];
+    CU(cudaMemcpy(h, d, sizeof h, cudaMemcpyDeviceToHost));
+    cudaFree(d);
+    out[0] = h[0];
+    out[1] = h[1];
+    out[2] = h[2];
+    return RTC_OK;
+}
+
 int rtc_probe_random_direction(int device, const uint32_t *states, int32_t n, float *out, uint32_t *out_states)
 {
     if (n < 0 || (n > 0 && (!states || !out || !out_states)))

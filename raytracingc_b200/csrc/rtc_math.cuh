@@ -21,6 +21,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "rtc_normal_fast.cuh"
+#include "rtc_powf.cuh"
+
 namespace rtc {
 
 struct f3 {
@@ -92,20 +95,41 @@ __device__ __forceinline__ uint32_t rng_next(uint32_t &state)
 }
 __device__ __forceinline__ float rng_to_unit(uint32_t r)
 {
-    double q = (double)r;
-    return (float)(__fma_rn(q, 2.3283064365386963e-10, q) * 2.3283064365386963e-10);
+    // (double)r, exactly, without the I2F.F64 conversion (5 issue clocks on the XU pipe): 2^52 + r has r in its low word
+    const double q = __dsub_rn(__hiloint2double(0x43300000, (int)r), 4503599627370496.0);
+    return (float)__dmul_rn(__fma_rn(q, 2.3283064365386963e-10, q), 2.3283064365386963e-10);
 }
 __device__ __forceinline__ float random_value(uint32_t &state) { return rng_to_unit(rng_next(state)); }
 
 // RandomValueNormalDistrubtion (moremath.c:98-103): all in double, narrowed
 // three times exactly where the reference's `float` locals narrow.
+// The reference's own sequence with the device's double libm: the definition of the result, and the slow path below.
+__device__ __forceinline__ float normal_from_draws_exact(float u1, float u2)
+{
+    float theta = (float)__dmul_rn(6.2831853, (double)u1); // 2 * 3.14159265, folded in double
+#if defined(RTC_WHATIF_FAST_SHADE) || defined(RTC_WHATIF_FAST_NORMAL) // TIMING EXPERIMENT ONLY (wrong images)
+    return sqrtf(-2.0f * __logf(u2)) * __cosf(theta);
+#endif
+    float rho = (float)__dsqrt_rn(__dmul_rn(-2.0, log((double)u2)));
+    return (float)__dmul_rn((double)rho, cos((double)theta));
+}
+
+// ---- the same float, cheaper: rtc_normal_fast.cuh (tailored double approximations + a Ziv test; falls back to the above) ----
+__device__ __forceinline__ float normal_from_draws(float u1, float u2)
+{
+#ifndef RTC_NORMAL_EXACT_ONLY
+    float v;
+    if (nf::normal_fast(u1, u2, v))
+        return v;
+#endif
+    return normal_from_draws_exact(u1, u2);
+}
+
 __device__ __forceinline__ float random_normal(uint32_t &state)
 {
     float u1 = random_value(state); // theta's draw comes first
     float u2 = random_value(state);
-    float theta = (float)__dmul_rn(6.2831853, (double)u1); // 2 * 3.14159265, folded in double
-    float rho = (float)__dsqrt_rn(__dmul_rn(-2.0, log((double)u2)));
-    return (float)__dmul_rn((double)rho, cos((double)theta));
+    return normal_from_draws(u1, u2);
 }
 // RandomDiretion (moremath.c:105-109): x, then y, then z, then normalized.
 // The call unit of the FP64 island: state in, {direction, state bits} out, all in registers.
@@ -135,19 +159,26 @@ struct SkyParams {
     int sun_skip_ok; // host: sunFocus >= 0 and sunIntensity finite (see environment_light)
 };
 
-// glibc's powf is < 1 ulp; CUDA's powf is several ulp, so evaluate in double
-// and narrow.
-// The double-precision evaluation only has to be far more accurate than a float ulp (glibc's own powf is off by up to
-// ~0.52 ulp, so agreement in the last bit is statistical either way): for a finite positive base and a finite
-// non-zero exponent it is exp2(y * log2(x)) in plain double -- relative error ~2^-46 for |y log2 x| < 64, i.e. one
-// more float in 2^21 rounded differently than by the exactly rounded power -- which is a third of the instructions
-// of CUDA's double pow (that one carries log2(x) in double-double to be accurate to 2 ulp OF A DOUBLE).  Everything
-// else (zero, infinite, negative or NaN base, zero exponent) takes pow() itself.
+// powf as the reference's libm computes it: rtc_powf.cuh restates glibc 2.39's algorithm (two small tables, ~20 FP64
+// instructions, one narrowing) and is bit-identical to it on every argument tried (2 * 10^9 on the host, 10^6 sky
+// directions on the device).  Round 1 evaluated exp2(y * log2(x)) with CUDA's double libm instead: ~3.7 times the
+// issue slots, and one sky value in 4000 off by one ulp.  Zero, negative, infinite or NaN bases and zero, infinite
+// or NaN exponents take pow() in double (IEEE special values; never on the sky's path, see environment_light).
 __device__ __noinline__ float xpowf(float x, float y)
 {
-#ifndef RTC_POW_LIBM
+#if defined(RTC_WHATIF_FAST_SHADE) || defined(RTC_WHATIF_FAST_POW) // TIMING EXPERIMENT ONLY (wrong images)
+    return __powf(x, y);
+#endif
+#ifdef RTC_POW_ROUND1 // A/B only: round 1's evaluation (correctly rounded, so NOT always glibc's float)
     if (x > 0.0f && x < __int_as_float(0x7f800000) && y != 0.0f && fabsf(y) < 1e30f)
         return (float)exp2((double)y * log2((double)x));
+#elif !defined(RTC_POW_LIBM)
+    const uint32_t ix = __float_as_uint(x);
+    if (ix - 1u < 0x7f7fffffu && y != 0.0f && fabsf(y) < __int_as_float(0x7f800000)) { // 0 < x < inf, y finite and non-zero
+        // (a subnormal x: scaled by 2^23 and the exponent taken back, modulo 2^32, as glibc does)
+        const uint32_t ib = ix >= 0x00800000u ? ix : __float_as_uint(__fmul_rn(x, 0x1p23f)) - (23u << 23);
+        return pw::powf_glibc_bits(ib, (double)y);
+    }
 #endif
     return (float)pow((double)x, (double)y);
 }
