@@ -133,10 +133,32 @@ __device__ __forceinline__ float random_normal(uint32_t &state)
 }
 // RandomDiretion (moremath.c:105-109): x, then y, then z, then normalized.
 // The call unit of the FP64 island: state in, {direction, state bits} out, all in registers.
+__device__ __noinline__ float normal_exact_call(float u1, float u2) { return normal_from_draws_exact(u1, u2); }
+
 __device__ __noinline__ float4 random_direction(uint32_t state)
 {
-    // one copy of the FP64 code executed three times: the smaller instruction footprint beats the overlap of three
-    // inlined chains (measured, C4 path kernel: 4.15 -> 3.95 ms; the shading code is instruction-fetch bound)
+#if !defined(RTC_NORMALS_LOOP) && !defined(RTC_NORMAL_EXACT_ONLY)
+    // the six draws first (a serial but cheap chain), then the three fast paths as independent instruction streams --
+    // a deviate is a chain of ~45 dependent FP64 instructions, three of them interleave: 960 clocks for a lone warp
+    // against 1660 looped, 470 against 497 issue clocks (profiles/r2_shade_probe.txt), C4 frame -1 % -- and ONE
+    // out-of-line copy of the exact sequence for whichever of them declined
+    float u[6];
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+        u[i] = random_value(state);
+    float x, y, z;
+    const bool kx = nf::normal_fast(u[0], u[1], x), ky = nf::normal_fast(u[2], u[3], y), kz = nf::normal_fast(u[4], u[5], z);
+    if (!(kx && ky && kz)) {
+        if (!kx)
+            x = normal_exact_call(u[0], u[1]);
+        if (!ky)
+            y = normal_exact_call(u[2], u[3]);
+        if (!kz)
+            z = normal_exact_call(u[4], u[5]);
+    }
+#else
+    // one copy of the FP64 code executed three times (with the libm sequence inline, round 1, the smaller instruction
+    // footprint beat the overlap of three inlined chains: C4 path kernel 4.15 -> 3.95 ms)
     float x = 0.f, y = 0.f, z = 0.f;
 #ifdef RTC_NORMALS_UNROLLED
 #pragma unroll
@@ -148,6 +170,7 @@ __device__ __noinline__ float4 random_direction(uint32_t state)
         y = z;
         z = random_normal(state);
     }
+#endif
     f3 v = xnormalize(mk3(x, y, z));
     return make_float4(v.x, v.y, v.z, __uint_as_float(state));
 }
