@@ -50,6 +50,29 @@ def test_environment_light_bits_at_scale():
     assert not bad.any(), f"{bad.sum()} of {len(dirs)} sky values differ, first for direction {dirs[bad][0]}"
 
 
+@pytest.mark.parametrize("focus,intensity", [(0.5, 0.75), (3.0, 2.0), (300.0, 0.75), (5000.0, 10.0), (0.0, 1.0)])
+def test_environment_light_other_sun_exponents(focus, intensity):
+    """powf(d, sunFocus) over its whole range -- small and huge exponents (underflow to subnormals and to zero for d < 1,
+    overflow for the d slightly above 1 that un-normalised bounce directions give), the zero exponent -- against the
+    reference's function on glibc, bit for bit (NaNs: both NaN)."""
+    from raytracingc_b200 import api
+    rng = np.random.default_rng(int(focus * 10) + 1)
+    sky = api.make_scene(sun_focus=focus, sun_intensity=intensity)
+    sun = np.array([sky.normalizedSunDirection.x, sky.normalizedSunDirection.y, sky.normalizedSunDirection.z], dtype=np.float64)
+    sun /= np.linalg.norm(sun)
+    d = rng.normal(size=(1 << 17, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    near = sun + rng.normal(size=(1 << 17, 3)) * rng.choice([1e-1, 1e-2, 1e-3, 1e-4], size=(1 << 17, 1))
+    near /= np.linalg.norm(near, axis=1, keepdims=True)
+    long_ = near[:8192] * rng.uniform(1.0, 1.2, (8192, 1))  # d > 1: lerps of unit vectors can be longer than 1 too
+    dirs = np.concatenate([d, near, -near[:8192], long_]).astype(np.float32)
+    want = _oracle().environment_light_batch(dirs, sky)
+    got = api.probe_environment_light(dirs, sky)
+    same = (got.view(np.uint32) == want.view(np.uint32)) | (np.isnan(got) & np.isnan(want))
+    bad = ~same.all(axis=1)
+    assert not bad.any(), f"{bad.sum()} of {len(dirs)} sky values differ, first for direction {dirs[bad][0]}: {got[bad][0]} != {want[bad][0]}"
+
+
 def test_normal_deviate_fast_path_equals_the_exact_sequence():
     """The Ziv-checked fast evaluation of RandomValueNormalDistrubtion (rtc_normal_fast.cuh) against the reference's own
     sequence on 2^27 generator states spread over the state space (tools/normal_selfcheck.py runs all 2^32:
