@@ -90,7 +90,7 @@ RTC_NF_FN bool narrow_checked(double v, double &out)
     return (d < 0 ? -d : d) > ZIV_ULPS;
 }
 
-// (double)(float)(6.2831853 * (double)u1), u1 = the float with bits b1 in (0, 1]: the reference's theta, EXACTLY (round
+// (double)(float)(6.2831853 * (double)u1), u1 = the normal float with bits b1, in [2^-32, 1]: the reference's theta, EXACTLY (round
 // to nearest, ties to even, at bit 29 of the exactly rounded double product; theta >= 1.4e-9 is a normal float)
 RTC_NF_FN double theta_as_double(uint32_t b1)
 {
@@ -175,8 +175,9 @@ RTC_NF_FN bool normal_fast(float u1, float u2, float &out)
     const bool ok1 = narrow_checked(sqrt_m2log(b2), rho);
     const bool ok2 = narrow_checked(rho * cos_0_2pi(theta_as_double(b1)), res);
     out = (float)res; // exact: res has float precision and |res| in [1e-12, 7]
-    // u1 in (0, 1], u2 in [2^-32, 1); anything else (u1 = 0, u2 = 0 or 1, NaN) is the exact sequence's business
-    return ok1 && ok2 && (b1 - 1u) < 0x3F800000u && (b2 - 0x2F800000u) < 0x10000000u;
+    // u1 in [2^-32, 1], u2 in [2^-32, 1) -- every non-zero draw of the generator; anything else (0, 1 for u2, a
+    // subnormal, which widen_bits does not handle, a NaN) is the exact sequence's business
+    return ok1 && ok2 && (b1 - 0x2F800000u) <= 0x10000000u && (b2 - 0x2F800000u) < 0x10000000u;
 }
 
 } // namespace nf
