@@ -14,9 +14,10 @@
 //
 // Second version.  The first one (short polynomials, but float<->double conversions wherever a float seed or a
 // narrowing was needed: 19 F2F + FRND + F2I + I2F per deviate) was proven exact and measured NO faster than the libm
-// sequence: conversions and MUFU share the 16-lane XU pipe (8 issue cycles per warp instruction), which it saturated.
+// sequence: FP64 arithmetic is cheap on this part (DFMA: 1.6 issue clocks per warp instruction) but conversions, FRND and
+// MUFU share the XU pipe at 5 - 6.5 clocks each (profiles/r2_shade_probe.txt), which that version saturated.
 // This one does every widening, narrowing, rounding test and integer conversion on the bit patterns (integer pipe):
-// 2 MUFU + 1 F2F per deviate.
+// 2 MUFU + 1 F2F per deviate; its double constants sit in the constant bank (see K[] below).
 //
 // Host-compilable: tools/normal_fast_host.cpp defines RTC_NF_HOST and the few intrinsics used here.
 #pragma once
