@@ -4,8 +4,8 @@
 //     theta = (float)(6.2831853 * u1);  rho = (float)sqrt(-2 log(u2));  return (float)(rho * cos(theta));
 // rtc_math.cuh's normal_from_draws_exact IS that sequence and defines the result.  It costs ~70 FP64 instructions and
 // a dozen conversions per deviate, three deviates per hit.  This file computes the same two narrowings from tailored
-// double approximations with a PROVEN relative error below 2^-43 and accepts them only when that error cannot change
-// the float (a Ziv test): rounding is monotonic, so when every double within the margin of the approximation rounds to
+// double approximations with a relative error below 2^-43 (term-by-term bounds in the comments below) and accepts
+// them only when an error 30 times that cannot change the float (a Ziv test): rounding is monotonic, so when every double within the margin of the approximation rounds to
 // the same float, so does the reference's own libm value (within 2^-52 of the truth, inside the margin too).  Else --
 // about one deviate in 10^4, and for every input outside the ranges below -- the caller runs the exact sequence.
 // The generator has only 2^32 states, so rtc_probe_normal_selfcheck compares the two for EVERY pair of draws the
@@ -71,7 +71,8 @@ RTC_NF_CONST double K[] = {
 };
 
 // distance (in ulps of the double) that an approximation must keep from a float rounding boundary to be accepted:
-// 2^14 ulps is a relative 2^-39 .. 2^-38, more than 30 times the proven error of the values tested below
+// 2^14 ulps is a relative 2^-39 .. 2^-38, more than 30 times the error bound of the values tested below.  (The
+// result does not rest on that bound: every pair of draws the generator can make has been enumerated, see the top.)
 constexpr int ZIV_ULPS = 1 << 14;
 
 // (double)f for a positive normal float f, from its bits (exponent re-biased, mantissa shifted): exact
